@@ -1,0 +1,385 @@
+// Blind rotation (tfhe-rs blind_rotate_assign / cmux / add_external_product_assign; SURVEY.md
+// 8(a1) rows a1.1, a1.5, a1.6, a1.7) for k = 1, N = 2048, one PBS level, as one sm_100a kernel:
+//   modulus switch -> LUT accumulator (closed form, already rotated by X^{-b~}) -> n CMUX
+//   iterations on an f64 negacyclic FFT -> sample extract.
+//
+// FFT design ("32x32 four-step, one warp per polynomial"):
+//   A real polynomial p of N = 2048 coefficients is folded to 1024 complex points
+//   z_j = p_j + i p_{j+1024} and evaluated at the roots x_k = e^{i pi (4k+1)/N} of X^N + 1:
+//       X[k] = sum_j z_j e^{2 pi i j (k + 1/4)/1024},   j = n1 + 32 n2,  k = 32 k1 + k2.
+//   Column pass (lane = n1, 32 values n2 in registers): shifted 32-point DFT = constant pre-twist
+//   c_{n2} = e^{2 pi i n2/128} + plain DFT-32 codelet.  Twiddle T[k2][n1] = e^{2 pi i n1 (k2+1/4)/1024}.
+//   Transpose through shared memory.  Row pass (lane = k2, 32 values n1 in registers): DFT-32.
+//   The negacyclic twist is therefore folded into compile-time constants and the twiddle table.
+//   The inverse runs the same passes backwards with conjugate factors; 1/1024 lives in the BSK.
+//
+// One ciphertext = 2 warps (64 threads): warp w owns accumulator polynomial w (0 = mask, 1 = body)
+// for the coefficient-domain work and the column passes; for the row passes warp w owns
+// frequencies k2 in [16w, 16w+16) of BOTH polynomials (lanes 0-15: poly 0, lanes 16-31: poly 1), so
+// the 2x2 GGSW contraction needs only one shfl_xor(16) exchange per frequency.
+//
+// A CTA holds kCtPerCta ciphertext slots that share the twiddle table; slots synchronise with
+// named barriers (64 threads) and fetch ciphertexts from a global work counter (persistent CTAs).
+#include "fhs_internal.cuh"
+#include "fft32_codelets.cuh"
+
+namespace fhs {
+namespace {
+
+constexpr int kCtPerCta = 3;
+constexpr int kThreads = 64 * kCtPerCta;
+constexpr int kTile = 32 * kTStride;  // complex elements in one padded 32x32 tile
+
+__constant__ double kPreRe[32] = FHS_PRETWIST_RE;
+__constant__ double kPreIm[32] = FHS_PRETWIST_IM;
+
+struct SlotSmem {
+    uint64_t acc[2][kN];     // accumulator GLWE: [0] mask polynomial, [1] body polynomial
+    double2 S[2][kTile];     // transpose tiles, one per polynomial: S[p][k2 * 33 + n1]
+    uint16_t amod[768];      // modulus-switched mask elements of the current ciphertext
+    unsigned int cur;        // index of the current ciphertext
+    unsigned int pad[3];
+};
+struct Smem {
+    double2 T[kTile];        // T[k2 * 33 + n1] = e^{2 pi i n1 (k2 + 1/4) / 1024}
+    SlotSmem slot[kCtPerCta];
+};
+static_assert(sizeof(Smem) <= 227 * 1024, "shared memory budget");
+
+__device__ __forceinline__ void slot_bar(int slot) {
+    asm volatile("bar.sync %0, 64;" ::"r"(slot + 1) : "memory");
+}
+
+// exact int32 -> double without the conversion pipe
+__device__ __forceinline__ double int_to_double(int d) {
+    return __hiloint2double(0x43300000, d ^ (int)0x80000000) - 4503601774854144.0;
+}
+
+// tfhe SignedDecomposer(base_log 23, level 1): closest representable, then one signed digit in
+// [-2^22, 2^22].
+__device__ __forceinline__ int pbs_digit(uint64_t x) {
+    const uint32_t hi = (uint32_t)(x >> 32);
+    const uint32_t s = (((hi >> 8) + 1u) >> 1) & 0x7FFFFFu;
+    return (int)s - (int)((s > 0x400000u) ? 0x800000u : 0u);
+}
+
+// Value in integer torus units (|v| < 2^115) -> v mod 2^64, rounded to nearest.
+__device__ __forceinline__ uint64_t f64_to_torus(double v) {
+    const double M = 1.24615124604835863e35;  // 1.5 * 2^116: ulp = 2^64
+    const double r = (v + M) - M;             // v rounded to a multiple of 2^64
+    return (uint64_t)__double2ll_rn(v - r);   // exact difference in [-2^63, 2^63]
+}
+
+// a1.5 pbs_modulus_switch for N = 2048: ((x >> 51) + 1) >> 1, reduced mod 2N.
+__device__ __forceinline__ uint32_t modswitch(uint64_t x) {
+    return (uint32_t)((((x >> 51) + 1ull) >> 1) & (uint64_t)(2 * kN - 1));
+}
+
+// a1.1 + initial rotation (SURVEY.md A.8 closed form): coefficient j of X^{-bt} * LUT_f.
+__device__ __forceinline__ uint64_t lut_coeff(const uint64_t *__restrict__ tab, uint32_t j,
+                                              uint32_t bt, int log_box, uint64_t delta) {
+    const uint32_t v = (j + bt + (1u << (log_box - 1))) & (2 * kN - 1);
+    const uint64_t f = tab[(v & (kN - 1)) >> log_box] * delta;
+    return (v & kN) ? (0ull - f) : f;
+}
+
+// Column pass, forward: inputs in BR5 slots -> slot k2 holds Y'[n1 = lane][k2].
+__device__ __forceinline__ void fwd_cols(double (&xr)[32], double (&xi)[32],
+                                         const double2 *__restrict__ T, int lane) {
+    fft32_pos(xr, xi);
+#pragma unroll
+    for (int k2 = 0; k2 < 32; k2++) {
+        const double2 t = T[k2 * kTStride + lane];
+        const double a = xr[k2], b = xi[k2];
+        xr[k2] = a * t.x - b * t.y;
+        xi[k2] = a * t.y + b * t.x;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+blind_rotate_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__restrict__ lut_id,
+                    const uint64_t *__restrict__ lut_tables, const double2 *__restrict__ bsk_f,
+                    const double2 *__restrict__ twiddle_g, uint64_t *__restrict__ lwe_out,
+                    unsigned int *__restrict__ counter, unsigned int batch, int n_lwe, int log_box,
+                    uint64_t delta) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
+    const int slot = threadIdx.x >> 6;
+    const int w = (threadIdx.x >> 5) & 1;
+    const int lane = threadIdx.x & 31;
+    SlotSmem &ss = sm.slot[slot];
+    const int table_len = kN >> log_box;
+
+    for (int t = threadIdx.x; t < kTile; t += kThreads) sm.T[t] = twiddle_g[t];
+    __syncthreads();
+
+    // row-pass role of this thread
+    const int rp = lane >> 4;                  // polynomial handled in the row passes
+    const int rk2 = 16 * w + (lane & 15);      // frequency residue k2 handled in the row passes
+    uint64_t *__restrict__ P = ss.acc[w];
+
+    for (;;) {
+        if ((threadIdx.x & 63) == 0) ss.cur = atomicAdd(counter, 1u);
+        slot_bar(slot);
+        const unsigned int ct = ss.cur;
+        if (ct >= batch) break;
+        const uint64_t *__restrict__ lwe = lwe_small + (size_t)ct * (n_lwe + 1);
+        for (int t = threadIdx.x & 63; t < n_lwe; t += 64) ss.amod[t] = (uint16_t)modswitch(lwe[t]);
+        const uint32_t bt = modswitch(lwe[n_lwe]);
+        if (w == 0) {
+#pragma unroll 8
+            for (int m = 0; m < kN / 32; m++) P[lane + 32 * m] = 0ull;
+        } else {
+            const uint64_t *__restrict__ tab = lut_tables + (size_t)lut_id[ct] * table_len;
+#pragma unroll 8
+            for (int m = 0; m < kN / 32; m++)
+                P[lane + 32 * m] = lut_coeff(tab, lane + 32 * m, bt, log_box, delta);
+        }
+        slot_bar(slot);
+
+        for (int i = 0; i < n_lwe; i++) {
+            const uint32_t a = ss.amod[i];
+            if (a == 0) continue;  // uniform over the slot's 64 threads
+
+            double xr[32], xi[32];
+            // ---- (X^a - 1) * acc_w, signed digit, pre-twist: inputs of the column pass ----
+            {
+                const uint32_t base = (uint32_t)(lane - (int)a) & (2 * kN - 1);
+#pragma unroll
+                for (int m = 0; m < 32; m++) {
+                    const uint32_t idx0 = (base + 32 * m) & (2 * kN - 1);
+                    const uint32_t idx1 = (idx0 + kH) & (2 * kN - 1);
+                    const uint64_t own0 = P[lane + 32 * m];
+                    const uint64_t own1 = P[lane + 32 * m + kH];
+                    const uint64_t r0 = P[idx0 & (kN - 1)];
+                    const uint64_t r1 = P[idx1 & (kN - 1)];
+                    const uint64_t m0 = (idx0 & kN) ? ~0ull : 0ull;
+                    const uint64_t m1 = (idx1 & kN) ? ~0ull : 0ull;
+                    const double d0 = int_to_double(pbs_digit((r0 ^ m0) - m0 - own0));
+                    const double d1 = int_to_double(pbs_digit((r1 ^ m1) - m1 - own1));
+                    if (m == 0) {
+                        xr[FHS_BR5(m)] = d0;
+                        xi[FHS_BR5(m)] = d1;
+                    } else {
+                        xr[FHS_BR5(m)] = d0 * kPreRe[m] - d1 * kPreIm[m];
+                        xi[FHS_BR5(m)] = d0 * kPreIm[m] + d1 * kPreRe[m];
+                    }
+                }
+            }
+            fwd_cols(xr, xi, sm.T, lane);
+            // ---- transpose: S[w][k2][n1 = lane] ----
+            __syncwarp();  // this warp's inverse-pass reads of plane w (previous iteration) are done
+            {
+                double2 *__restrict__ Sw = ss.S[w];
+#pragma unroll
+                for (int k2 = 0; k2 < 32; k2++) Sw[k2 * kTStride + lane] = make_double2(xr[k2], xi[k2]);
+            }
+            slot_bar(slot);
+            {
+                const double2 *__restrict__ Sr = ss.S[rp] + rk2 * kTStride;
+#pragma unroll
+                for (int n1 = 0; n1 < 32; n1++) {
+                    const double2 v = Sr[n1];
+                    xr[FHS_BR5(n1)] = v.x;
+                    xi[FHS_BR5(n1)] = v.y;
+                }
+            }
+            fft32_pos(xr, xi);  // slot k1: D_rp[32 k1 + rk2]
+            // ---- GGSW contraction: F_c = D_0 B[0][c] + D_1 B[1][c] ----
+            {
+                const double2 *__restrict__ Bp =
+                    bsk_f + ((((size_t)i * 32) * 2 + w) * 32 + lane) * 2;
+                double fr[32], fi[32];
+#pragma unroll
+                for (int k1 = 0; k1 < 32; k1++) {
+                    const double2 bs = __ldg(Bp + (size_t)k1 * 128);      // row rp, column 1 - rp
+                    const double2 bk = __ldg(Bp + (size_t)k1 * 128 + 1);  // row rp, column rp
+                    const double dr = xr[k1], di = xi[k1];
+                    const double sr = dr * bs.x - di * bs.y;
+                    const double si = dr * bs.y + di * bs.x;
+                    const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
+                    const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
+                    fr[FHS_BR5(k1)] = fma(dr, bk.x, fma(-di, bk.y, gr));
+                    fi[FHS_BR5(k1)] = fma(dr, bk.y, fma(di, bk.x, gi));
+                }
+#pragma unroll
+                for (int q = 0; q < 32; q++) {
+                    xr[q] = fr[q];
+                    xi[q] = fi[q];
+                }
+            }
+            // ---- inverse row pass (over k1 -> n1), conjugate twiddle ----
+            fft32_neg(xr, xi);
+            {
+                const double2 *__restrict__ Tr = sm.T + rk2 * kTStride;
+#pragma unroll
+                for (int n1 = 0; n1 < 32; n1++) {
+                    const double2 t = Tr[n1];
+                    const double a0 = xr[n1], b0 = xi[n1];
+                    xr[n1] = a0 * t.x + b0 * t.y;
+                    xi[n1] = b0 * t.x - a0 * t.y;
+                }
+            }
+            __syncwarp();  // forward-pass reads of these rows (by this warp) are done
+            {
+                double2 *__restrict__ Sq = ss.S[rp] + rk2 * kTStride;
+#pragma unroll
+                for (int n1 = 0; n1 < 32; n1++) Sq[n1] = make_double2(xr[n1], xi[n1]);
+            }
+            slot_bar(slot);
+            {
+                const double2 *__restrict__ Sw = ss.S[w];
+#pragma unroll
+                for (int k2 = 0; k2 < 32; k2++) {
+                    const double2 v = Sw[k2 * kTStride + lane];
+                    xr[FHS_BR5(k2)] = v.x;
+                    xi[FHS_BR5(k2)] = v.y;
+                }
+            }
+            // ---- inverse column pass (over k2 -> n2), conjugate pre-twist, add as torus ----
+            fft32_neg(xr, xi);
+#pragma unroll
+            for (int m = 0; m < 32; m++) {
+                double ur, ui;
+                if (m == 0) {
+                    ur = xr[m];
+                    ui = xi[m];
+                } else {
+                    ur = xr[m] * kPreRe[m] + xi[m] * kPreIm[m];
+                    ui = xi[m] * kPreRe[m] - xr[m] * kPreIm[m];
+                }
+                P[lane + 32 * m] += f64_to_torus(ur);
+                P[lane + 32 * m + kH] += f64_to_torus(ui);
+            }
+            __syncwarp();  // accumulator updates visible to this warp's rotated reads
+        }
+
+        // ---- a1.7 sample extract at coefficient 0 ----
+        uint64_t *__restrict__ out = lwe_out + (size_t)ct * (kN + 1);
+        if (w == 0) {
+#pragma unroll 8
+            for (int m = 0; m < kN / 32; m++) {
+                const int j = lane + 32 * m;
+                out[j] = (j == 0) ? P[0] : (0ull - P[kN - j]);
+            }
+        } else if (lane == 0) {
+            out[kN] = P[0];
+        }
+    }
+}
+
+// Forward transform of the standard-domain BSK into the layout the kernel above reads:
+//   bsk_f[(((i*32 + k1)*2 + w)*32 + lane)*2 + slot],  rp = lane >> 4, k2 = 16 w + (lane & 15),
+//   slot 0 = GGSW row rp, column 1-rp ("send"), slot 1 = row rp, column rp ("keep"),
+//   value = (1/1024) * FFT(signed torus polynomial)[32 k1 + k2].
+constexpr int kXfWarps = 4;
+struct XfSmem {
+    double2 T[kTile];
+    double2 S[kXfWarps][kTile];
+};
+
+__global__ void __launch_bounds__(32 * kXfWarps)
+bsk_transform_kernel(const uint64_t *__restrict__ bsk, double2 *__restrict__ bsk_f,
+                     const double2 *__restrict__ twiddle_g, int n_polys) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    XfSmem &sm = *reinterpret_cast<XfSmem *>(smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int t = threadIdx.x; t < kTile; t += 32 * kXfWarps) sm.T[t] = twiddle_g[t];
+    __syncthreads();
+    const int q = blockIdx.x * kXfWarps + warp;
+    if (q >= n_polys) return;
+    const int i = q >> 2, r = (q >> 1) & 1, c = q & 1;
+    const uint64_t *__restrict__ P = bsk + (size_t)q * kN;
+    double xr[32], xi[32];
+#pragma unroll
+    for (int m = 0; m < 32; m++) {
+        const double d0 = __ll2double_rn((long long)P[lane + 32 * m]);
+        const double d1 = __ll2double_rn((long long)P[lane + 32 * m + kH]);
+        xr[FHS_BR5(m)] = d0 * kPreRe[m] - d1 * kPreIm[m];
+        xi[FHS_BR5(m)] = d0 * kPreIm[m] + d1 * kPreRe[m];
+    }
+    fwd_cols(xr, xi, sm.T, lane);
+    double2 *__restrict__ S = sm.S[warp];
+#pragma unroll
+    for (int k2 = 0; k2 < 32; k2++) S[k2 * kTStride + lane] = make_double2(xr[k2], xi[k2]);
+    __syncwarp();
+#pragma unroll
+    for (int n1 = 0; n1 < 32; n1++) {
+        const double2 v = S[lane * kTStride + n1];
+        xr[FHS_BR5(n1)] = v.x;
+        xi[FHS_BR5(n1)] = v.y;
+    }
+    fft32_pos(xr, xi);
+    const int k2 = lane;
+    const int ww = k2 >> 4, lp = (r << 4) | (k2 & 15), sl = (c == r) ? 1 : 0;
+    const double sc = 1.0 / 1024.0;
+#pragma unroll
+    for (int k1 = 0; k1 < 32; k1++) {
+        bsk_f[((((size_t)i * 32 + k1) * 2 + ww) * 32 + lp) * 2 + sl] =
+            make_double2(xr[k1] * sc, xi[k1] * sc);
+    }
+}
+
+__global__ void build_lut_kernel(const uint64_t *__restrict__ table, uint64_t *__restrict__ acc,
+                                 int log_box, uint64_t delta) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < kN) {
+        acc[j] = 0ull;
+        acc[kN + j] = lut_coeff(table, (uint32_t)j, 0u, log_box, delta);
+    }
+}
+
+int ilog2(uint32_t x) {
+    int l = 0;
+    while ((1u << l) < x) l++;
+    return l;
+}
+
+}  // namespace
+
+size_t bsk_fourier_elems(const Ctx *c) { return (size_t)c->n * 32 * 2 * 32 * 2; }
+
+int launch_bsk_transform(Ctx *c, const uint64_t *d_bsk_std) {
+    const int n_polys = (int)c->n * 4;
+    FHS_CUDA(cudaFuncSetAttribute(bsk_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)sizeof(XfSmem)));
+    bsk_transform_kernel<<<(n_polys + kXfWarps - 1) / kXfWarps, 32 * kXfWarps, sizeof(XfSmem),
+                           c->stream>>>(d_bsk_std, c->d_bsk_f, c->d_twiddle, n_polys);
+    c->launches++;
+    FHS_CUDA(cudaGetLastError());
+    return FHS_OK;
+}
+
+int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc) {
+    const int log_box = ilog2(kN / c->space);
+    const uint64_t delta = (1ull << 63) / c->space;
+    build_lut_kernel<<<kN / 256, 256, 0, c->stream>>>(d_table, d_acc, log_box, delta);
+    c->launches++;
+    FHS_CUDA(cudaGetLastError());
+    return FHS_OK;
+}
+
+int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
+                        const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
+    if (batch == 0) return FHS_OK;
+    static bool attr_set = false;
+    if (!attr_set) {
+        FHS_CUDA(cudaFuncSetAttribute(blind_rotate_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(Smem)));
+        attr_set = true;
+    }
+    const int log_box = ilog2(kN / c->space);
+    const uint64_t delta = (1ull << 63) / c->space;
+    FHS_CUDA(cudaMemsetAsync(c->d_counter, 0, sizeof(unsigned int), c->stream));
+    size_t ctas = (batch + kCtPerCta - 1) / kCtPerCta;
+    if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
+    blind_rotate_kernel<<<(unsigned)ctas, kThreads, sizeof(Smem), c->stream>>>(
+        d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, c->d_counter,
+        (unsigned int)batch, (int)c->n, log_box, delta);
+    c->launches++;
+    FHS_CUDA(cudaGetLastError());
+    return FHS_OK;
+}
+
+}  // namespace fhs

@@ -1,0 +1,63 @@
+// Internal declarations shared by the CUDA translation units of libfhs_cuda.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include "../../include/fhs_cuda.h"
+
+namespace fhs {
+
+// Compile-time geometry of the blind-rotation kernels (PARAM_MESSAGE_2_CARRY_2_KS_PBS family:
+// k = 1, N = 2048, one PBS level).  Other sets are rejected at fhs_upload_keys.
+constexpr int kN = 2048;         // polynomial size
+constexpr int kH = kN / 2;       // complex points per polynomial (folded real FFT)
+constexpr int kTStride = 33;     // padded row stride (complex elements) of 32x32 smem tiles
+
+struct Ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    fhs_params p{};
+    bool has_keys = false;
+    uint32_t n = 0, big = 0;       // lwe_dim, k*N
+    uint32_t space = 0;            // message_modulus * carry_modulus
+    // device key material
+    uint64_t *d_ksk = nullptr;     // [k*N][ks_level (digit order, least significant first)][n+1]
+    uint64_t *d_ksk_corr = nullptr;// [n+1]  2^(base_log-1) * sum of all KSK rows (unsigned-digit offset)
+    double2 *d_bsk_f = nullptr;    // Fourier BSK, layout in blind_rotate.cu
+    double2 *d_twiddle = nullptr;  // [32][33] inter-pass twiddles T[k2][n1]
+    // scratch
+    uint64_t *d_small = nullptr;   // [cap][n+1] keyswitched ciphertexts
+    uint64_t *d_in = nullptr;      // [cap][big+1] staging for host-buffer calls
+    uint64_t *d_out = nullptr;
+    uint32_t *d_lut_id = nullptr;
+    uint64_t *d_tables = nullptr;
+    size_t cap = 0, cap_tables = 0;
+    unsigned int *d_counter = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool ev_valid[2] = {false, false};
+    uint64_t launches = 0;
+    int sm_count = 0;
+};
+
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);
+
+#define FHS_CUDA(expr)                                            \
+    do {                                                          \
+        cudaError_t _e = (expr);                                  \
+        if (_e != cudaSuccess) return ::fhs::cuda_fail(_e, #expr); \
+    } while (0)
+
+// keyswitch.cu
+int launch_keyswitch(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_small);
+int launch_ksk_prepare(Ctx *c, const uint64_t *d_ksk_raw, int level_order);
+// blind_rotate.cu
+int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
+                        const uint64_t *d_tables, size_t batch, uint64_t *d_out);
+int launch_bsk_transform(Ctx *c, const uint64_t *d_bsk_std);
+int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc);
+size_t bsk_fourier_elems(const Ctx *c);
+
+}  // namespace fhs

@@ -1,0 +1,195 @@
+"""ctypes binding of include/fhs_cuda.h (libfhs_cuda.so).  Host-side plumbing only."""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "libfhs_cuda.so")
+
+u64p = ctypes.POINTER(ctypes.c_uint64)
+u32p = ctypes.POINTER(ctypes.c_uint32)
+
+
+class FhsError(RuntimeError):
+    pass
+
+
+class Params(ctypes.Structure):
+    """fhs_params: tfhe-rs ClassicPBSParameters subset (reference src/lib.rs:31,45,50)."""
+    _fields_ = [(n, ctypes.c_uint32) for n in (
+        "lwe_dim", "glwe_dim", "poly_size", "pbs_base_log", "pbs_level", "ks_base_log", "ks_level",
+        "message_modulus", "carry_modulus", "reserved")]
+
+
+# every symbol include/fhs_cuda.h declares
+EXPORTS = [
+    "fhs_default_params", "fhs_last_error", "fhs_version", "fhs_ctx_create", "fhs_ctx_destroy",
+    "fhs_ctx_set_stream", "fhs_ctx_synchronize", "fhs_upload_keys", "fhs_ks_pbs_batch",
+    "fhs_ks_pbs_batch_dev", "fhs_keyswitch_batch", "fhs_keyswitch_batch_dev", "fhs_build_lut",
+    "fhs_pbs_batch", "fhs_pbs_batch_dev", "fhs_last_kernel_ms", "fhs_launch_count",
+]
+
+_lib = None
+
+
+def lib_path():
+    return _LIB
+
+
+def load_library():
+    """Loads libfhs_cuda.so; raises FhsError if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB):
+        raise FhsError(f"{_LIB} is missing: build it with `python -m fhe_string_b200.build` "
+                       "(there is no CPU fallback)")
+    L = ctypes.CDLL(_LIB)
+    vp = ctypes.c_void_p
+    sz = ctypes.c_size_t
+    L.fhs_default_params.argtypes = [ctypes.POINTER(Params)]
+    L.fhs_default_params.restype = None
+    L.fhs_last_error.restype = ctypes.c_char_p
+    L.fhs_version.restype = ctypes.c_int
+    L.fhs_ctx_create.argtypes = [ctypes.c_int, ctypes.POINTER(vp)]
+    L.fhs_ctx_destroy.argtypes = [vp]
+    L.fhs_ctx_destroy.restype = None
+    L.fhs_ctx_set_stream.argtypes = [vp, vp]
+    L.fhs_ctx_synchronize.argtypes = [vp]
+    L.fhs_upload_keys.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, vp]
+    L.fhs_ks_pbs_batch.argtypes = [vp, vp, vp, vp, sz, sz, vp]
+    L.fhs_ks_pbs_batch_dev.argtypes = [vp, vp, vp, vp, sz, sz, vp]
+    L.fhs_keyswitch_batch.argtypes = [vp, vp, sz, vp]
+    L.fhs_keyswitch_batch_dev.argtypes = [vp, vp, sz, vp]
+    L.fhs_build_lut.argtypes = [vp, vp, vp]
+    L.fhs_pbs_batch.argtypes = [vp, vp, vp, vp, sz, sz, vp]
+    L.fhs_pbs_batch_dev.argtypes = [vp, vp, vp, vp, sz, sz, vp]
+    L.fhs_last_kernel_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    L.fhs_launch_count.argtypes = [vp]
+    L.fhs_launch_count.restype = ctypes.c_uint64
+    _lib = L
+    return L
+
+
+def default_params():
+    p = Params()
+    load_library().fhs_default_params(ctypes.byref(p))
+    return p
+
+
+def _np(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a, a.ctypes.data
+
+
+class Engine:
+    """One context on one GPU (fhs_ctx).  Mirrors the role of the reference's ServerKey
+    (src/server_key.rs:12-33): holds the device-resident key material and evaluates levels."""
+
+    def __init__(self, device=0):
+        self.L = load_library()
+        h = ctypes.c_void_p()
+        self._check(self.L.fhs_ctx_create(int(device), ctypes.byref(h)))
+        self.h = h
+        self.device = device
+        self.p = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise FhsError(f"fhs error {rc}: {self.L.fhs_last_error().decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.fhs_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- keys ----
+    def upload_keys(self, params, ksk, bsk, ksk_level_order=0):
+        p = Params()
+        for name, _ in Params._fields_:
+            setattr(p, name, int(getattr(params, name)))
+        ksk, kp = _np(ksk, np.uint64)
+        bsk, bp = _np(bsk, np.uint64)
+        big = p.glwe_dim * p.poly_size
+        assert ksk.size == big * p.ks_level * (p.lwe_dim + 1), "ksk size"
+        assert bsk.size == p.lwe_dim * p.pbs_level * (p.glwe_dim + 1) ** 2 * p.poly_size, "bsk size"
+        self._check(self.L.fhs_upload_keys(self.h, ctypes.byref(p), kp, int(ksk_level_order), bp))
+        self.p = p
+        self.big = big + 1
+        self.small = p.lwe_dim + 1
+        self.space = p.message_modulus * p.carry_modulus
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self.L.fhs_ctx_set_stream(self.h, ctypes.c_void_p(cuda_stream_ptr or 0)))
+
+    def synchronize(self):
+        self._check(self.L.fhs_ctx_synchronize(self.h))
+
+    # ---- host-buffer entry points ----
+    def ks_pbs(self, cts, lut_id, tables, out=None):
+        cts, cp = _np(cts, np.uint64)
+        cts = cts.reshape(-1, self.big)
+        lut_id, lp = _np(lut_id, np.uint32)
+        tables, tp = _np(tables, np.uint64)
+        tables = tables.reshape(-1, self.space)
+        assert lut_id.size == len(cts)
+        assert lut_id.size == 0 or int(lut_id.max()) < len(tables)
+        if out is None:
+            out = np.empty_like(cts)
+        self._check(self.L.fhs_ks_pbs_batch(self.h, cp, lp, tp, len(tables), len(cts),
+                                             out.ctypes.data))
+        return out
+
+    def ks_pbs_ptr(self, in_ptr, lut_ptr, tab_ptr, n_luts, batch, out_ptr):
+        """Host pointers (e.g. pinned torch tensors)."""
+        self._check(self.L.fhs_ks_pbs_batch(self.h, in_ptr, lut_ptr, tab_ptr, n_luts, batch, out_ptr))
+
+    def keyswitch(self, cts):
+        cts, cp = _np(cts, np.uint64)
+        cts = cts.reshape(-1, self.big)
+        out = np.empty((len(cts), self.small), dtype=np.uint64)
+        self._check(self.L.fhs_keyswitch_batch(self.h, cp, len(cts), out.ctypes.data))
+        return out
+
+    def build_lut(self, table):
+        table, tp = _np(table, np.uint64)
+        assert table.size == self.space
+        out = np.empty((self.p.glwe_dim + 1) * self.p.poly_size, dtype=np.uint64)
+        self._check(self.L.fhs_build_lut(self.h, tp, out.ctypes.data))
+        return out
+
+    def pbs(self, small, lut_id, tables):
+        small, sp = _np(small, np.uint64)
+        small = small.reshape(-1, self.small)
+        lut_id, lp = _np(lut_id, np.uint32)
+        tables, tp = _np(tables, np.uint64)
+        tables = tables.reshape(-1, self.space)
+        out = np.empty((len(small), self.big), dtype=np.uint64)
+        self._check(self.L.fhs_pbs_batch(self.h, sp, lp, tp, len(tables), len(small),
+                                          out.ctypes.data))
+        return out
+
+    # ---- device-pointer entry points (ints from torch .data_ptr()) ----
+    def ks_pbs_dev(self, d_in, d_lut_id, d_tables, n_luts, batch, d_out):
+        self._check(self.L.fhs_ks_pbs_batch_dev(self.h, d_in, d_lut_id, d_tables, n_luts, batch, d_out))
+
+    def keyswitch_dev(self, d_in, batch, d_out):
+        self._check(self.L.fhs_keyswitch_batch_dev(self.h, d_in, batch, d_out))
+
+    def pbs_dev(self, d_small, d_lut_id, d_tables, n_luts, batch, d_out):
+        self._check(self.L.fhs_pbs_batch_dev(self.h, d_small, d_lut_id, d_tables, n_luts, batch, d_out))
+
+    def last_kernel_ms(self):
+        ms = (ctypes.c_float * 2)()
+        self._check(self.L.fhs_last_kernel_ms(self.h, ms))
+        return float(ms[0]), float(ms[1])
+
+    def launch_count(self):
+        return int(self.L.fhs_launch_count(self.h))

@@ -1,0 +1,116 @@
+/*
+ * fhs_cuda.h -- C ABI of the B200-native batched KS-PBS engine under fhe_string.
+ *
+ * The reference has no FFI for this path: fhe_string calls tfhe::integer::ServerKey methods
+ * (`k.k.<op>`, /root/reference/src/server_key.rs:12-33 and every call site listed in SURVEY.md
+ * Appendix C, e.g. src/ciphertext/compare.rs:32, src/ciphertext/search.rs:33-41), and each of those
+ * ends in tfhe-rs `keyswitch_programmable_bootstrap_assign` on one block at a time.  This header is
+ * the boundary a `fhe_string_cuda` crate would bind instead (INTEGRATION.md shows the Rust
+ * `extern "C"` block): one call evaluates a whole LEVEL of independent LUT evaluations.
+ *
+ * Conventions: every function returns 0 on success and a negative fhs_status on failure; the
+ * message is available from fhs_last_error().  Nothing unwinds across this boundary.  The caller
+ * owns all host buffers; the library owns all device memory.  A context is bound to one GPU and
+ * is NOT thread-safe; use one context per GPU (one process per GPU in the multi-GPU layout).
+ * There is no CPU fallback: without a CUDA device fhs_ctx_create fails with FHS_ERR_CUDA.
+ */
+#ifndef FHS_CUDA_H
+#define FHS_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    FHS_OK = 0,
+    FHS_ERR_INVALID = -1,     /* bad argument / unsupported parameter set */
+    FHS_ERR_CUDA = -2,        /* CUDA runtime error, see fhs_last_error */
+    FHS_ERR_NO_KEYS = -3,     /* keys not uploaded yet */
+    FHS_ERR_OOM = -4,
+    FHS_ERR_COMM = -5         /* NCCL error */
+} fhs_status;
+
+/* tfhe-rs ClassicPBSParameters as used by the reference (src/lib.rs:31,45,50:
+ * PARAM_MESSAGE_2_CARRY_2_KS_PBS): n=742, k=1, N=2048, pbs 23/1, ks 3/5, msg 4, carry 4. */
+typedef struct {
+    uint32_t lwe_dim;
+    uint32_t glwe_dim;
+    uint32_t poly_size;
+    uint32_t pbs_base_log;
+    uint32_t pbs_level;
+    uint32_t ks_base_log;
+    uint32_t ks_level;
+    uint32_t message_modulus;
+    uint32_t carry_modulus;
+    uint32_t reserved;
+} fhs_params;
+
+typedef struct fhs_ctx fhs_ctx;
+
+/* KSK row order inside one input-coefficient block (version-sensitive in tfhe-rs). */
+#define FHS_KSK_LEVEL_MSB_FIRST 0 /* rows stored level 1 (most significant) .. level l  (tfhe-rs 0.5) */
+#define FHS_KSK_LEVEL_LSB_FIRST 1 /* rows stored level l .. level 1 */
+
+void fhs_default_params(fhs_params *p);
+const char *fhs_last_error(void);
+int fhs_version(void);
+
+/* Context on CUDA device `device` (ordinal).  Replaces: construction of tfhe ServerKey state
+ * (src/server_key.rs:12-17). */
+int fhs_ctx_create(int device, fhs_ctx **out);
+void fhs_ctx_destroy(fhs_ctx *ctx);
+/* Run all work of this context on an existing CUDA stream (cudaStream_t as void*); NULL = the
+ * context's own stream.  Lets a host framework time launches with its own events. */
+int fhs_ctx_set_stream(fhs_ctx *ctx, void *cuda_stream);
+int fhs_ctx_synchronize(fhs_ctx *ctx);
+
+/* Upload server key material once per GPU (north_star item 3).  Replaces the key held by
+ * tfhe::integer::ServerKey (src/lib.rs:64-72).
+ *   ksk : u64 [k*N][ks_level][n+1]                 (level order per `ksk_level_order`)
+ *   bsk : u64 [n][pbs_level][k+1][k+1][N]          standard (coefficient) domain GGSW rows
+ * The BSK is transformed to the Fourier domain on the GPU in the layout the blind-rotation kernel
+ * consumes; the KSK is re-tiled to digit order. */
+int fhs_upload_keys(fhs_ctx *ctx, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
+                    const uint64_t *bsk);
+
+/* One level of independent LUT evaluations, host buffers (copies inside the call).
+ * Replaces B calls of shortint apply_lookup_table (tfhe keyswitch_programmable_bootstrap_assign),
+ * reached from e.g. src/ciphertext/compare.rs:32,74,130-132, src/ciphertext/logic.rs:13-65.
+ *   lwe_in  : u64 [B][k*N+1]   big-key LWE blocks (mask || body)
+ *   lut_id  : u32 [B]          row of lut_tables for block b
+ *   lut_tables : u64 [n_luts][message_modulus*carry_modulus]  f(x) values (not scaled by Delta)
+ *   lwe_out : u64 [B][k*N+1] */
+int fhs_ks_pbs_batch(fhs_ctx *ctx, const uint64_t *lwe_in, const uint32_t *lut_id,
+                     const uint64_t *lut_tables, size_t n_luts, size_t batch, uint64_t *lwe_out);
+/* Same, all pointers are DEVICE pointers on the context's GPU; asynchronous on its stream. */
+int fhs_ks_pbs_batch_dev(fhs_ctx *ctx, const uint64_t *d_lwe_in, const uint32_t *d_lut_id,
+                         const uint64_t *d_lut_tables, size_t n_luts, size_t batch,
+                         uint64_t *d_lwe_out);
+
+/* Verification entry points for the bit-exact tiers. */
+/* tfhe keyswitch_lwe_ciphertext on a batch: [B][k*N+1] -> [B][n+1]; host buffers. */
+int fhs_keyswitch_batch(fhs_ctx *ctx, const uint64_t *lwe_in, size_t batch, uint64_t *lwe_small_out);
+int fhs_keyswitch_batch_dev(fhs_ctx *ctx, const uint64_t *d_lwe_in, size_t batch,
+                            uint64_t *d_lwe_small_out);
+/* tfhe generate_lookup_table: 16-entry table -> trivial GLWE accumulator [(k+1)][N] (mask 0),
+ * produced by the same device code the blind rotation uses (closed form, rotation 0). */
+int fhs_build_lut(fhs_ctx *ctx, const uint64_t *table, uint64_t *acc_out);
+/* Blind rotation + sample extract only (no keyswitch): small LWE [B][n+1] -> big LWE [B][k*N+1]. */
+int fhs_pbs_batch(fhs_ctx *ctx, const uint64_t *lwe_small_in, const uint32_t *lut_id,
+                  const uint64_t *lut_tables, size_t n_luts, size_t batch, uint64_t *lwe_out);
+int fhs_pbs_batch_dev(fhs_ctx *ctx, const uint64_t *d_lwe_small_in, const uint32_t *d_lut_id,
+                      const uint64_t *d_lut_tables, size_t n_luts, size_t batch,
+                      uint64_t *d_lwe_out);
+
+/* Device-time of the most recent *_batch call's kernels in milliseconds (CUDA events on the
+ * context's stream): [0]=keyswitch, [1]=blind rotation (+LUT build, sample extract). */
+int fhs_last_kernel_ms(fhs_ctx *ctx, float *ms2);
+/* Number of kernels this context has launched so far. */
+uint64_t fhs_launch_count(fhs_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FHS_CUDA_H */

@@ -1,0 +1,97 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on seeded inputs."""
+import numpy as np
+import pytest
+
+from conftest import bench_tables
+
+pytestmark = pytest.mark.gpu
+
+
+def _mixed_inputs(keyset, n, seed):
+    rng = np.random.default_rng(seed)
+    msgs = rng.integers(0, 16, n)
+    cts = keyset.encrypt(msgs, seed=seed)
+    return msgs, cts
+
+
+def test_keyswitch_bit_exact(engine, keyset):
+    rng = np.random.default_rng(5)
+    msgs, cts = _mixed_inputs(keyset, 40, 5)
+    triv = keyset.trivial(np.arange(16))
+    garbage = rng.integers(0, 2**64, size=(9, keyset.big), dtype=np.uint64)
+    edge = np.zeros((4, keyset.big), dtype=np.uint64)
+    edge[0, :] = np.uint64(0xFFFFFFFFFFFFFFFF)
+    edge[1, :] = np.uint64(0x8000000000000000)
+    edge[2, :] = np.uint64(0x7FFFFFFFFFFFFFFF)
+    edge[3, ::2] = np.uint64(0x0000FFFFFFFFFFFF)
+    allc = np.concatenate([cts, triv, garbage, edge])
+    got = engine.keyswitch(allc)
+    want = keyset.keyswitch(allc)
+    assert got.shape == want.shape
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("batch", [1, 3, 29, 150, 600])
+def test_keyswitch_tile_shapes(engine, keyset, batch):
+    rng = np.random.default_rng(batch)
+    cts = rng.integers(0, 2**64, size=(batch, keyset.big), dtype=np.uint64)
+    got = engine.keyswitch(cts)
+    idx = sorted(set([0, batch - 1, batch // 2]))
+    want = keyset.keyswitch(cts[idx])
+    assert np.array_equal(got[idx], want)
+
+
+def test_build_lut_bit_exact(engine, keyset):
+    rng = np.random.default_rng(9)
+    tabs = list(bench_tables()) + [rng.integers(0, 16, 16).astype(np.uint64) for _ in range(4)]
+    tabs.append(rng.integers(0, 2**64, 16, dtype=np.uint64))
+    for t in tabs:
+        assert np.array_equal(engine.build_lut(t), keyset.build_lut(t))
+
+
+def test_ks_pbs_decrypts_and_noise(engine, keyset):
+    tables = bench_tables()
+    n = 512
+    msgs, cts = _mixed_inputs(keyset, n, 42)
+    lut_id = (np.arange(n) % 8).astype(np.uint32)
+    out = engine.ks_pbs(cts, lut_id, tables)
+    want = tables[lut_id, msgs]
+    assert np.array_equal(keyset.decrypt(out), want)
+    err = keyset.phase_error(out, want)
+    # analytic output-noise estimate: sigma ~ 2.1e-5 .. 2.5e-5
+    assert np.std(err) < 4e-5
+    assert np.abs(err).max() < 2.0**-9  # half a box is 2^-6
+
+
+def test_blind_rotate_close_to_oracle(engine, keyset):
+    """Same small-key LWE in, GPU vs oracle blind rotation: identical up to FFT rounding noise."""
+    tables = bench_tables()
+    n = 24
+    msgs, cts = _mixed_inputs(keyset, n, 7)
+    small = keyset.keyswitch(cts)
+    lut_id = (np.arange(n) % 8).astype(np.uint32)
+    got = engine.pbs(small, lut_id, tables)
+    want = keyset.ks_pbs_batch(cts, lut_id, tables)
+    assert np.array_equal(keyset.decrypt(got), keyset.decrypt(want))
+    d = (got - want).astype(np.int64).astype(np.float64) / 2.0**64
+    # coefficient-wise distance of the two LWE ciphertexts: both carry independent rounding noise
+    assert np.abs(d).max() < 2.0**-10
+    ph = keyset.phase_error(got, tables[lut_id, msgs]) - keyset.phase_error(want, tables[lut_id, msgs])
+    assert np.std(ph) < 6e-5
+
+
+def test_trivial_and_padding_bit(engine, keyset):
+    """Trivial ciphertexts are accepted; padding bit set gives the negacyclic -LUT."""
+    tables = bench_tables()
+    triv = keyset.trivial(np.arange(32))  # 16..31 have the padding bit set
+    lut_id = np.full(32, 7, dtype=np.uint32)
+    out = engine.ks_pbs(triv, lut_id, tables)
+    dec = keyset.decrypt(out)  # values mod 32 (padding bit included)
+    f = tables[7]
+    want = np.array([f[x] if x < 16 else (32 - int(f[x - 16])) % 32 for x in range(32)], dtype=np.uint64)
+    assert np.array_equal(dec, want)
+
+
+def test_empty_batch(engine, keyset):
+    out = engine.ks_pbs(np.zeros((0, keyset.big), np.uint64), np.zeros(0, np.uint32), bench_tables())
+    assert out.shape == (0, keyset.big)
