@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py -- batched KS-PBS microbench (BASELINE.json configs[1]): 4096 LUT evaluations,
+PARAM_MESSAGE_2_CARRY_2_KS_PBS, per GPU.
+
+A "step" is one pass of the hot path (keyswitch -> blind rotation -> sample extract) over one batch
+of 4096 synthetic encrypted blocks per GPU.  `value` is device-timed with inputs resident in HBM;
+`e2e` goes through the host-buffer C-ABI call (fhs_ks_pbs_batch) with pinned host memory, H2D and
+D2H inside the timed region.  `--impl reference` times the CPU restatement of the reference's path
+(oracle/, OpenMP over ciphertexts = the rayon stand-in) on the box's host cores.
+
+Multi-GPU: one process per GPU (torchrun), full key replica per GPU (broadcast over NCCL), the
+batch is sharded by ciphertext with no data-path collective (weak scaling: 4096 per GPU).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BATCH = 4096
+FLOP_PER_PBS = 194_510_848          # 742 * 262144
+METRIC = "KS-PBS throughput (PBS/s), 4096 LUT evals per GPU, PARAM_MESSAGE_2_CARRY_2_KS_PBS"
+
+
+def bench_tables():
+    t = np.zeros((8, 16), dtype=np.uint64)
+    for x in range(16):
+        t[0, x] = x
+        t[1, x] = x % 4
+        t[2, x] = x // 4
+        t[3, x] = 1 if x == 5 else 0
+        t[4, x] = 1 if x >= 9 else 0
+        t[5, x] = 1 if (x // 4) == (x % 4) else 0
+        t[6, x] = ((x // 4) * (x % 4)) % 4
+        t[7, x] = 2 if x < 8 else 0
+    return t
+
+
+def synth_inputs(ks, batch, seed):
+    """Synthetic encrypted blocks: valid big-key LWE encryptions of uniform 4-bit messages."""
+    rng = np.random.default_rng(seed)
+    msgs = rng.integers(0, 16, batch)
+    s = ks.glwe_sk().astype(bool)
+    mask = rng.integers(0, 2**64, size=(batch, ks.big - 1), dtype=np.uint64)
+    noise = np.rint(rng.normal(0.0, ks.p.glwe_std * 2.0**64, batch)).astype(np.int64).astype(np.uint64)
+    with np.errstate(over="ignore"):
+        body = mask[:, s].sum(axis=1, dtype=np.uint64) + msgs.astype(np.uint64) * np.uint64(ks.delta) + noise
+    cts = np.concatenate([mask, body[:, None]], axis=1)
+    lut_id = (np.arange(batch) % 8).astype(np.uint32)
+    return msgs, cts, lut_id
+
+
+class ClockSampler:
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip().splitlines()
+                if out:
+                    f = [x.strip() for x in out[0].split(",")]
+                    self.samples.append(float(f[0]))
+                    self.max_mhz = float(f[1])
+                    for nm, v in zip(names, f[2:]):
+                        if v.lower().startswith("active"):
+                            self.reasons.add(nm)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        self._t.join(timeout=6)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def cpu_baseline(ks, tables, threads, target_seconds=12.0):
+    """Oracle (port of the reference's CPU path) on a bounded sample of the same workload."""
+    from oracle import oracle as O
+    threads = threads or O.lib().orc_max_threads()
+    msgs, cts, lut_id = synth_inputs(ks, 2 * threads, seed=4242)
+    t0 = time.perf_counter()
+    ks.ks_pbs_batch(cts, lut_id, tables, threads=threads)
+    dt = time.perf_counter() - t0
+    per = dt / 2.0                                  # seconds per "round" of `threads` PBS
+    rounds = max(2, int(target_seconds / max(per, 1e-3)))
+    n = min(BATCH, rounds * threads)
+    msgs, cts, lut_id = synth_inputs(ks, n, seed=4243)
+    t0 = time.perf_counter()
+    out = ks.ks_pbs_batch(cts, lut_id, tables, threads=threads)
+    dt = time.perf_counter() - t0
+    ok = bool(np.array_equal(ks.decrypt(out), tables[lut_id, msgs]))
+    return {"value": n / dt, "unit": "PBS/s", "cores": int(threads), "kind": "port",
+            "sample": f"{n} of the 4096 KS-PBS of one step, OpenMP over ciphertexts, {dt:.1f} s, "
+                      f"decrypt-correct={ok}"}
+
+
+def run_reference(args):
+    """CPU arm: the oracle port of the reference's tfhe-rs path (the Rust reference cannot be built
+    here: no cargo, tfhe crate not vendored).  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle as O
+    ks = O.Keyset(seed=1)
+    tables = bench_tables()
+    threads = O.lib().orc_max_threads()
+    n = 4 * threads                                   # bounded sample of one 4096-block step
+    msgs, cts, lut_id = synth_inputs(ks, n, seed=7)
+    for _ in range(args.warmup):
+        ks.ks_pbs_batch(cts[:threads], lut_id[:threads], tables, threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ks.ks_pbs_batch(cts, lut_id, tables, threads=threads)
+    dt = time.perf_counter() - t0
+    v = args.steps * n / dt
+    sample = f"{n} KS-PBS per step (bounded sample of the 4096-block batch), {threads} OpenMP threads"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "PBS/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64+u64",
+        "data": "synthetic",
+        "config": {"workload": "ks_pbs_microbench_4096_PARAM_MESSAGE_2_CARRY_2_KS_PBS",
+                   "batch_per_gpu": BATCH, "reference_arm": "CPU port of the tfhe-rs 0.5 KS-PBS (oracle/)"},
+        "cpu_baseline": {"value": v, "unit": "PBS/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "PBS/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import fhe_string_b200 as F
+    from oracle import oracle as O   # key generation + the cpu_baseline leg only
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    warm = max(args.warmup, 3)
+    batch = args.batch
+
+    # ---- keys: rank 0 generates (client side, CPU), broadcast over NCCL, upload per GPU ----
+    ks = O.Keyset(seed=1)            # deterministic: every rank could regenerate, but the product
+    p = ks.p                         # path is "broadcast keys over NVLink" (north_star)
+    if world > 1:
+        if rank == 0:
+            ksk_t = torch.from_numpy(ks.ksk().view(np.int64)).to(dev)
+            bsk_t = torch.from_numpy(ks.bsk().view(np.int64)).to(dev)
+        else:
+            ksk_t = torch.empty(p.glwe_dim * p.poly_size * p.ks_level * (p.lwe_dim + 1), dtype=torch.int64, device=dev)
+            bsk_t = torch.empty(p.lwe_dim * 4 * p.poly_size, dtype=torch.int64, device=dev)
+        dist.broadcast(ksk_t, 0)
+        dist.broadcast(bsk_t, 0)
+        ksk = ksk_t.cpu().numpy().view(np.uint64)
+        bsk = bsk_t.cpu().numpy().view(np.uint64)
+        del ksk_t, bsk_t
+    else:
+        ksk, bsk = ks.ksk(), ks.bsk()
+    eng = F.Engine(local)
+    eng.upload_keys(p, ksk, bsk, ksk_level_order=0)
+    stream = torch.cuda.current_stream()
+    eng.set_stream(stream.cuda_stream)
+    tables = bench_tables()
+
+    # ---- synthetic inputs: this rank's shard; 3 rotating input buffers (201 MB > L2) ----
+    nbuf = 3
+    host_in, dev_in, msgs_l = [], [], []
+    for b in range(nbuf):
+        msgs, cts, lut_id = synth_inputs(ks, batch, seed=1000 * (rank + 1) + b)
+        hp = torch.from_numpy(cts.view(np.int64)).pin_memory()
+        host_in.append(hp)
+        dev_in.append(hp.to(dev, non_blocking=True))
+        msgs_l.append(msgs)
+    lut_host = torch.from_numpy(lut_id.astype(np.int32)).pin_memory()
+    tab_host = torch.from_numpy(tables.view(np.int64).copy()).pin_memory()
+    d_lut = lut_host.to(dev)
+    d_tab = tab_host.to(dev)
+    d_out = torch.empty((batch, eng.big), dtype=torch.int64, device=dev)
+    host_out = torch.empty((batch, eng.big), dtype=torch.int64).pin_memory()
+    torch.cuda.synchronize()
+
+    def step_dev(i):
+        eng.ks_pbs_dev(dev_in[i % nbuf].data_ptr(), d_lut.data_ptr(), d_tab.data_ptr(), len(tables),
+                       batch, d_out.data_ptr())
+
+    def step_e2e(i):
+        eng.ks_pbs_ptr(host_in[i % nbuf].data_ptr(), lut_host.data_ptr(), tab_host.data_ptr(),
+                       len(tables), batch, host_out.data_ptr())
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ----
+    for i in range(warm):
+        step_dev(i)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = eng.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ks_ms = br_ms = 0.0
+    e0.record(stream)
+    for i in range(args.steps):
+        step_dev(i)
+    e1.record(stream)
+    barrier()
+    launches = eng.launch_count() - launches0
+    ms_total = e0.elapsed_time(e1)
+    # per-kernel durations (CUDA events recorded inside the library around each launch)
+    for i in range(min(args.steps, 5)):
+        step_dev(i)
+        torch.cuda.synchronize()
+        a, b = eng.last_kernel_ms()
+        ks_ms += a
+        br_ms += b
+    ks_ms /= min(args.steps, 5)
+    br_ms /= min(args.steps, 5)
+    clocks = sampler.stop()
+
+    # correctness of the last device step (decrypt with the client key; not timed)
+    torch.cuda.synchronize()
+    last = (min(args.steps, 5) - 1) % nbuf
+    out_np = d_out.cpu().numpy().view(np.uint64)
+    ok_dev = bool(np.array_equal(ks.decrypt(out_np), tables[lut_id, msgs_l[last]]))
+
+    # ---- end-to-end timing through the host-buffer C ABI ----
+    for i in range(warm):
+        step_e2e(i)
+    barrier()
+    t_e2e0 = torch.cuda.Event(enable_timing=True)
+    t_e2e1 = torch.cuda.Event(enable_timing=True)
+    t_e2e0.record(stream)
+    for i in range(args.steps):
+        step_e2e(i)          # blocking call: H2D + kernels + D2H + stream sync inside
+    t_e2e1.record(stream)
+    barrier()
+    e2e_ms = t_e2e0.elapsed_time(t_e2e1)
+    out_np = host_out.numpy().view(np.uint64)
+    ok_e2e = bool(np.array_equal(ks.decrypt(out_np), tables[lut_id, msgs_l[(args.steps - 1) % nbuf]]))
+
+    # ---- max over ranks ----
+    if dist is not None:
+        t = torch.tensor([ms_total, e2e_ms, br_ms, ks_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, e2e_ms, br_ms, ks_ms = [float(x) for x in t.tolist()]
+        okt = torch.tensor([int(ok_dev and ok_e2e)], device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        ok_all = bool(okt.item())
+    else:
+        ok_all = ok_dev and ok_e2e
+
+    if rank == 0:
+        total = batch * world
+        value = total * args.steps / (ms_total * 1e-3)
+        e2e_val = total * args.steps / (e2e_ms * 1e-3)
+        fp64_peak = eng.measure_fp64_tflops()
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+        achieved_tf = batch * FLOP_PER_PBS / (br_ms * 1e-3) / 1e12
+        ks_bytes = 60_866_560 + batch * (16_392 + 5_944)
+        ks_gbs = ks_bytes / (ks_ms * 1e-3) / 1e9 if ks_ms > 0 else None
+        line = {
+            "metric": METRIC, "value": value, "unit": "PBS/s", "n_gpus": world, "steps": args.steps,
+            "warmup": warm, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64+u64", "data": "synthetic",
+            "config": {"workload": "ks_pbs_microbench_4096_PARAM_MESSAGE_2_CARRY_2_KS_PBS",
+                       "batch_per_gpu": batch, "luts": 8, "lwe_dim": 742, "poly_size": 2048,
+                       "parallelism": f"replica x{world}, batch sharded by ciphertext, no data-path collective",
+                       "l2": "3 rotating 67 MB input buffers + 67 MB output + 110 MB keys per step > 126 MB L2"},
+            "correct": ok_all,
+            "gpu_launches": int(launches),
+            "kernels_per_step": {"keyswitch_ms": ks_ms, "blind_rotate_ms": br_ms},
+            "roofline": {"bound": "fp64", "kernel": "blind_rotate_kernel", "achieved": achieved_tf,
+                         "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp64_peak,
+                         "traffic": None,
+                         "peak_source": "measured in this run: DFMA chains (fhs_measure_fp64_tflops); "
+                                        "MEASURED_PEAKS.json has no FP64 figure",
+                         "algorithmic": f"{FLOP_PER_PBS} flop/PBS x {batch} PBS per launch"},
+            "roofline_keyswitch": {"bound": "hbm", "kernel": "keyswitch_kernel", "achieved": ks_gbs,
+                                   "peak": hbm_peak, "unit": "GB/s",
+                                   "frac": (ks_gbs / hbm_peak) if ks_gbs else None,
+                                   "peak_source": hbm_src,
+                                   "algorithmic": f"{ks_bytes} B per launch (KSK once + B x (16392 + 5944))"},
+            "e2e": {"value": e2e_val, "unit": "PBS/s",
+                    "h2d_bytes_per_step": int(batch * eng.big * 8 + batch * 4 + tables.size * 8) * world,
+                    "d2h_bytes_per_step": int(batch * eng.big * 8) * world,
+                    "ms_per_step": e2e_ms / args.steps},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(ks, tables, 0)
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

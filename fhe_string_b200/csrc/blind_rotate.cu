@@ -29,6 +29,7 @@ namespace {
 constexpr int kCtPerCta = 3;
 constexpr int kThreads = 64 * kCtPerCta;
 constexpr int kTile = 32 * kTStride;  // complex elements in one padded 32x32 tile
+constexpr int kBskRing = 8;           // BSK frequency rows in flight per thread (register ring)
 
 __constant__ double kPreRe[32] = FHS_PRETWIST_RE;
 __constant__ double kPreIm[32] = FHS_PRETWIST_IM;
@@ -48,6 +49,16 @@ static_assert(sizeof(Smem) <= 227 * 1024, "shared memory budget");
 
 __device__ __forceinline__ void slot_bar(int slot) {
     asm volatile("bar.sync %0, 64;" ::"r"(slot + 1) : "memory");
+}
+
+// Streaming 16-byte BSK load.  asm volatile keeps the compiler from sinking the prefetch below the
+// barrier it is issued in front of (the point of the ring is to overlap L2 latency).
+__device__ __forceinline__ double2 ldg_stream(const double2 *p) {
+    double2 v;
+    asm volatile("ld.volatile.global.v2.f64 {%0, %1}, [%2];"
+                 : "=d"(v.x), "=d"(v.y)
+                 : "l"(p));
+    return v;
 }
 
 // exact int32 -> double without the conversion pipe
@@ -174,6 +185,15 @@ blind_rotate_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__re
 #pragma unroll
                 for (int k2 = 0; k2 < 32; k2++) Sw[k2 * kTStride + lane] = make_double2(xr[k2], xi[k2]);
             }
+            // BSK prefetch ring: the first kBskRing frequency rows are requested before the
+            // barrier and the row pass so their L2 latency is hidden behind the transpose + DFT-32.
+            const double2 *__restrict__ Bp = bsk_f + ((((size_t)i * 32) * 2 + w) * 32 + lane) * 2;
+            double2 bs[kBskRing], bk[kBskRing];
+#pragma unroll
+            for (int q = 0; q < kBskRing; q++) {
+                bs[q] = ldg_stream(Bp + (size_t)q * 128);      // GGSW row rp, column 1 - rp
+                bk[q] = ldg_stream(Bp + (size_t)q * 128 + 1);  // GGSW row rp, column rp
+            }
             slot_bar(slot);
             {
                 const double2 *__restrict__ Sr = ss.S[rp] + rk2 * kTStride;
@@ -186,26 +206,31 @@ blind_rotate_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__re
             }
             fft32_pos(xr, xi);  // slot k1: D_rp[32 k1 + rk2]
             // ---- GGSW contraction: F_c = D_0 B[0][c] + D_1 B[1][c] ----
+            // Result for frequency row k1 goes to slot BR5(k1) (input order of the inverse DFT-32):
+            // rows are visited so that a slot is overwritten only after its own row was consumed.
             {
-                const double2 *__restrict__ Bp =
-                    bsk_f + ((((size_t)i * 32) * 2 + w) * 32 + lane) * 2;
-                double fr[32], fi[32];
 #pragma unroll
                 for (int k1 = 0; k1 < 32; k1++) {
-                    const double2 bs = __ldg(Bp + (size_t)k1 * 128);      // row rp, column 1 - rp
-                    const double2 bk = __ldg(Bp + (size_t)k1 * 128 + 1);  // row rp, column rp
+                    const double2 cs = bs[k1 % kBskRing], ck = bk[k1 % kBskRing];
+                    if (k1 + kBskRing < 32) {
+                        bs[k1 % kBskRing] = ldg_stream(Bp + (size_t)(k1 + kBskRing) * 128);
+                        bk[k1 % kBskRing] = ldg_stream(Bp + (size_t)(k1 + kBskRing) * 128 + 1);
+                    }
                     const double dr = xr[k1], di = xi[k1];
-                    const double sr = dr * bs.x - di * bs.y;
-                    const double si = dr * bs.y + di * bs.x;
+                    const double sr = dr * cs.x - di * cs.y;
+                    const double si = dr * cs.y + di * cs.x;
                     const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
                     const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
-                    fr[FHS_BR5(k1)] = fma(dr, bk.x, fma(-di, bk.y, gr));
-                    fi[FHS_BR5(k1)] = fma(dr, bk.y, fma(di, bk.x, gi));
+                    xr[k1] = fma(dr, ck.x, fma(-di, ck.y, gr));
+                    xi[k1] = fma(dr, ck.y, fma(di, ck.x, gi));
                 }
+                // bit-reversal permutation of the 32 slots (register renaming only)
 #pragma unroll
                 for (int q = 0; q < 32; q++) {
-                    xr[q] = fr[q];
-                    xi[q] = fi[q];
+                    if (FHS_BR5(q) > q) {
+                        double t0 = xr[q]; xr[q] = xr[FHS_BR5(q)]; xr[FHS_BR5(q)] = t0;
+                        double t1 = xi[q]; xi[q] = xi[FHS_BR5(q)]; xi[FHS_BR5(q)] = t1;
+                    }
                 }
             }
             // ---- inverse row pass (over k1 -> n1), conjugate twiddle ----

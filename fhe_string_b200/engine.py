@@ -28,6 +28,7 @@ EXPORTS = [
     "fhs_ctx_set_stream", "fhs_ctx_synchronize", "fhs_upload_keys", "fhs_ks_pbs_batch",
     "fhs_ks_pbs_batch_dev", "fhs_keyswitch_batch", "fhs_keyswitch_batch_dev", "fhs_build_lut",
     "fhs_pbs_batch", "fhs_pbs_batch_dev", "fhs_last_kernel_ms", "fhs_launch_count",
+    "fhs_measure_fp64_tflops",
 ]
 
 _lib = None
@@ -68,6 +69,7 @@ def load_library():
     L.fhs_last_kernel_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     L.fhs_launch_count.argtypes = [vp]
     L.fhs_launch_count.restype = ctypes.c_uint64
+    L.fhs_measure_fp64_tflops.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     _lib = L
     return L
 
@@ -190,6 +192,11 @@ class Engine:
         ms = (ctypes.c_float * 2)()
         self._check(self.L.fhs_last_kernel_ms(self.h, ms))
         return float(ms[0]), float(ms[1])
+
+    def measure_fp64_tflops(self):
+        v = ctypes.c_double()
+        self._check(self.L.fhs_measure_fp64_tflops(self.h, ctypes.byref(v)))
+        return float(v.value)
 
     def launch_count(self):
         return int(self.L.fhs_launch_count(self.h))

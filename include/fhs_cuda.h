@@ -109,6 +109,9 @@ int fhs_pbs_batch_dev(fhs_ctx *ctx, const uint64_t *d_lwe_small_in, const uint32
 int fhs_last_kernel_ms(fhs_ctx *ctx, float *ms2);
 /* Number of kernels this context has launched so far. */
 uint64_t fhs_launch_count(fhs_ctx *ctx);
+/* Measured FP64 FMA throughput of the context's GPU in TFLOP/s (dependent-free DFMA chains, best
+ * of 4 after a warm-up): the roofline denominator of the blind-rotation kernel. */
+int fhs_measure_fp64_tflops(fhs_ctx *ctx, double *tflops_out);
 
 #ifdef __cplusplus
 }
