@@ -201,7 +201,11 @@ def main():
         ksk, bsk = ks.ksk(), ks.bsk()
     eng = F.Engine(local)
     eng.upload_keys(p, ksk, bsk, ksk_level_order=0)
-    stream = torch.cuda.current_stream()
+    # a non-default torch stream: its handle is non-NULL, so the library launches on exactly the
+    # stream the torch.cuda.Event timers below are recorded on
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     eng.set_stream(stream.cuda_stream)
     tables = bench_tables()
 

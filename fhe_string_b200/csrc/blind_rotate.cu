@@ -20,8 +20,11 @@
 //
 // A CTA holds kCtPerCta ciphertext slots that share the twiddle table; slots synchronise with
 // named barriers (64 threads) and fetch ciphertexts from a global work counter (persistent CTAs).
+#include <cstdlib>
+
 #include "fhs_internal.cuh"
 #include "fft32_codelets.cuh"
+#include "tmem.cuh"
 
 namespace fhs {
 namespace {
@@ -293,6 +296,320 @@ blind_rotate_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__re
     }
 }
 
+// =================================================================================================
+// v2: "lock-step CTA with TMEM": 4 ciphertext slots (8 compute warps) + 4 loader warps per CTA.
+//   * The accumulator lives in Tensor Memory: every compute thread owns 64 coefficients of its
+//     warp's polynomial as 128 lane-private 32-bit columns (64 high words, 64 low words).  Shared
+//     memory keeps only the HIGH 32 bits of each coefficient (the "hi plane", 16 KB per ciphertext)
+//     for the rotated reads of (X^a - 1) * acc: the signed digit needs the top 23 bits, and the
+//     dropped borrow perturbs the value being rounded by < 2^-32 (torus), far below the 2^-24
+//     rounding step of the decomposition itself (noise-bounded tier).
+//   * The Fourier BSK row of iteration i is shared by the 4 ciphertexts of the CTA: loader warp q
+//     (one per TMEM lane quarter) streams the 32 KB slice of role w = q & 1 from L2 into registers
+//     and parks it in TMEM columns [256, 512) of its quarter; compute warps pull 4 frequency rows
+//     (32 columns) at a time with tcgen05.ld.  Named barriers kBarFull / kBarFree hand the single
+//     buffer back and forth; the loads of slice i+1 are already in flight while slice i is consumed.
+//   * All compute warps advance through i in lock step (they meet at kBarFull every iteration), so
+//     one L2 read of the BSK serves 4 ciphertexts and the instruction stream is shared.
+constexpr int kSlots2 = 4;
+constexpr int kComputeThreads2 = 64 * kSlots2;   // 256
+constexpr int kLoaderThreads2 = 128;             // one loader warp per TMEM lane quarter
+constexpr int kThreads2 = kComputeThreads2 + kLoaderThreads2;
+constexpr int kBarFull = 5, kBarFree = 6;
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kTmemBskCol = 256;
+
+struct SlotSmem2 {
+    uint32_t hi[2][kN];      // high words of the accumulator polynomials
+    double2 S[2][kTile];     // transpose tiles
+    uint16_t amod[768];
+};
+struct Smem2 {
+    double2 T[kTile];
+    SlotSmem2 slot[kSlots2];
+    uint32_t tmem_base;
+    uint32_t pad[3];
+};
+static_assert(sizeof(Smem2) <= 227 * 1024, "shared memory budget (v2)");
+
+__device__ __forceinline__ void named_bar_sync(int id, int n) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int n) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+
+__device__ __forceinline__ int pbs_digit_hi(uint32_t hi) {
+    const uint32_t s = (((hi >> 8) + 1u) >> 1) & 0x7FFFFFu;
+    return (int)s - (int)((s > 0x400000u) ? 0x800000u : 0u);
+}
+
+__device__ __forceinline__ void ldg_b128(const void *p, uint32_t &a, uint32_t &b, uint32_t &c,
+                                         uint32_t &d) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(a), "=r"(b), "=r"(c), "=r"(d)
+                 : "l"(p));
+}
+
+__global__ void __launch_bounds__(kThreads2, 1)
+blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__restrict__ lut_id,
+                       const uint64_t *__restrict__ lut_tables, const double2 *__restrict__ bsk_f,
+                       const double2 *__restrict__ twiddle_g, uint64_t *__restrict__ lwe_out,
+                       unsigned int batch, int n_lwe, int log_box, uint64_t delta) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Smem2 &sm = *reinterpret_cast<Smem2 *>(smem_raw);
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    for (int t = threadIdx.x; t < kTile; t += kThreads2) sm.T[t] = twiddle_g[t];
+    if (warp == 0) tmem_alloc(&sm.tmem_base, kTmemCols);
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    const uint32_t tbase = sm.tmem_base + (((uint32_t)(warp & 3) * 32u) << 16);
+    const unsigned int n_groups = (batch + kSlots2 - 1) / kSlots2;
+
+    if (warp >= 2 * kSlots2) {
+        // =========================== BSK loader warps ===========================
+        // Register budget: the pool that setmaxnreg.inc draws from is what the loaders release, so
+        // (R_compute - 168) * 256 <= (168 - R_loader) * 128  ->  56 / 224.
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        const int role = warp & 1;  // lane quarter q = warp & 3 serves compute warps with w = q & 1
+        bool first = true;
+        for (unsigned int g = blockIdx.x; g < n_groups; g += gridDim.x) {
+            for (int i = 0; i < n_lwe; i++) {
+                const uint4 *__restrict__ src = reinterpret_cast<const uint4 *>(
+                    bsk_f + ((((size_t)i * 32) * 2 + role) * 32 + lane) * 2);
+#pragma unroll 1
+                for (int b = 0; b < 8; b++) {   // 4 frequency rows (32 columns) per batch
+                    uint32_t r[32];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const uint4 *p = src + (size_t)(4 * b + k) * 128;  // row stride 128 double2
+                        ldg_b128(p, r[8 * k + 0], r[8 * k + 1], r[8 * k + 2], r[8 * k + 3]);
+                        ldg_b128(p + 1, r[8 * k + 4], r[8 * k + 5], r[8 * k + 6], r[8 * k + 7]);
+                    }
+                    if (b == 0 && !first) {     // previous slice fully consumed?
+                        named_bar_sync(kBarFree, kThreads2);
+                        tmem_fence_after_sync();
+                    }
+                    tmem_st32(tbase + kTmemBskCol + 32 * b, r);
+                }
+                first = false;
+                tmem_wait_st();
+                tmem_fence_before_sync();
+                named_bar_arrive(kBarFull, kThreads2);
+            }
+        }
+    } else {
+        // =========================== compute warps ===========================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
+        const int slot = warp >> 1;
+        const int w = warp & 1;
+        SlotSmem2 &ss = sm.slot[slot];
+        const int table_len = kN >> log_box;
+        const int rp = lane >> 4;
+        const int rk2 = 16 * w + (lane & 15);
+        uint32_t *__restrict__ H = ss.hi[w];
+        const uint32_t tacc = tbase + (uint32_t)(warp >> 2) * 128u;  // hi words [0,64), lo words [64,128)
+        const uint32_t tbsk = tbase + kTmemBskCol;
+        const unsigned int last_group = ((n_groups - 1 - blockIdx.x) / gridDim.x) * gridDim.x + blockIdx.x;
+
+        for (unsigned int g = blockIdx.x; g < n_groups; g += gridDim.x) {
+            unsigned int ct = g * kSlots2 + slot;
+            if (ct >= batch) ct = batch - 1;  // idle slot of the last group: recompute the last one
+            const uint64_t *__restrict__ lwe = lwe_small + (size_t)ct * (n_lwe + 1);
+            for (int t = threadIdx.x & 63; t < n_lwe; t += 64) ss.amod[t] = (uint16_t)modswitch(lwe[t]);
+            {
+                // a1.1 + rotation by X^{-b~}: this thread's 64 coefficients -> TMEM + hi plane
+                const uint32_t bt = modswitch(lwe[n_lwe]);
+                const uint64_t *__restrict__ tab = lut_tables + (size_t)lut_id[ct] * table_len;
+                uint32_t vhi[64], vlo[64];
+#pragma unroll
+                for (int q = 0; q < 64; q++) {
+                    const int j = lane + 32 * (q >> 1) + kH * (q & 1);
+                    const uint64_t v = (w == 0) ? 0ull : lut_coeff(tab, (uint32_t)j, bt, log_box, delta);
+                    vhi[q] = (uint32_t)(v >> 32);
+                    vlo[q] = (uint32_t)v;
+                    H[j] = vhi[q];
+                }
+                tmem_st64(tacc, vhi);
+                tmem_st64(tacc + 64, vlo);
+                tmem_wait_st();
+            }
+            slot_bar(slot);  // amod + hi plane visible
+
+            for (int i = 0; i < n_lwe; i++) {
+                const uint32_t a = ss.amod[i];
+                double xr[32], xi[32];
+                // ---- (X^a - 1) * acc_w on high words, signed digit, pre-twist ----
+                {
+                    uint32_t own[64];
+                    tmem_ld64(tacc, own);
+                    const uint32_t base = (uint32_t)(lane - (int)a) & (2 * kN - 1);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int m = 0; m < 32; m++) {
+                        const uint32_t idx0 = (base + 32 * m) & (2 * kN - 1);
+                        const uint32_t idx1 = (idx0 + kH) & (2 * kN - 1);
+                        uint32_t r0 = H[idx0 & (kN - 1)];
+                        uint32_t r1 = H[idx1 & (kN - 1)];
+                        r0 = (idx0 & kN) ? ~r0 : r0;
+                        r1 = (idx1 & kN) ? ~r1 : r1;
+                        const double d0 = int_to_double(pbs_digit_hi(r0 - own[2 * m]));
+                        const double d1 = int_to_double(pbs_digit_hi(r1 - own[2 * m + 1]));
+                        if (m == 0) {
+                            xr[FHS_BR5(m)] = d0;
+                            xi[FHS_BR5(m)] = d1;
+                        } else {
+                            xr[FHS_BR5(m)] = d0 * kPreRe[m] - d1 * kPreIm[m];
+                            xi[FHS_BR5(m)] = d0 * kPreIm[m] + d1 * kPreRe[m];
+                        }
+                    }
+                }
+                fwd_cols(xr, xi, sm.T, lane);
+                {
+                    double2 *__restrict__ Sw = ss.S[w];
+#pragma unroll
+                    for (int k2 = 0; k2 < 32; k2++)
+                        Sw[k2 * kTStride + lane] = make_double2(xr[k2], xi[k2]);
+                }
+                slot_bar(slot);
+                {
+                    const double2 *__restrict__ Sr = ss.S[rp] + rk2 * kTStride;
+#pragma unroll
+                    for (int n1 = 0; n1 < 32; n1++) {
+                        const double2 v = Sr[n1];
+                        xr[FHS_BR5(n1)] = v.x;
+                        xi[FHS_BR5(n1)] = v.y;
+                    }
+                }
+                fft32_pos(xr, xi);
+                // ---- GGSW contraction against the BSK slice parked in TMEM ----
+                named_bar_sync(kBarFull, kThreads2);
+                tmem_fence_after_sync();
+#pragma unroll
+                for (int b = 0; b < 8; b++) {
+                    uint32_t br[32];
+                    tmem_ld32(tbsk + 32 * b, br);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const int k1 = 4 * b + k;
+                        const double csx = __hiloint2double((int)br[8 * k + 1], (int)br[8 * k + 0]);
+                        const double csy = __hiloint2double((int)br[8 * k + 3], (int)br[8 * k + 2]);
+                        const double ckx = __hiloint2double((int)br[8 * k + 5], (int)br[8 * k + 4]);
+                        const double cky = __hiloint2double((int)br[8 * k + 7], (int)br[8 * k + 6]);
+                        const double dr = xr[k1], di = xi[k1];
+                        const double sr = dr * csx - di * csy;
+                        const double si = dr * csy + di * csx;
+                        const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
+                        const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
+                        xr[k1] = fma(dr, ckx, fma(-di, cky, gr));
+                        xi[k1] = fma(dr, cky, fma(di, ckx, gi));
+                    }
+                }
+                if (!(g == last_group && i == n_lwe - 1)) {
+                    tmem_fence_before_sync();
+                    named_bar_arrive(kBarFree, kThreads2);
+                }
+#pragma unroll
+                for (int q = 0; q < 32; q++) {
+                    if (FHS_BR5(q) > q) {
+                        double t0 = xr[q]; xr[q] = xr[FHS_BR5(q)]; xr[FHS_BR5(q)] = t0;
+                        double t1 = xi[q]; xi[q] = xi[FHS_BR5(q)]; xi[FHS_BR5(q)] = t1;
+                    }
+                }
+                // ---- inverse row pass, conjugate twiddle, transpose back ----
+                fft32_neg(xr, xi);
+                {
+                    const double2 *__restrict__ Tr = sm.T + rk2 * kTStride;
+#pragma unroll
+                    for (int n1 = 0; n1 < 32; n1++) {
+                        const double2 t = Tr[n1];
+                        const double a0 = xr[n1], b0 = xi[n1];
+                        xr[n1] = a0 * t.x + b0 * t.y;
+                        xi[n1] = b0 * t.x - a0 * t.y;
+                    }
+                }
+                {
+                    double2 *__restrict__ Sq = ss.S[rp] + rk2 * kTStride;
+#pragma unroll
+                    for (int n1 = 0; n1 < 32; n1++) Sq[n1] = make_double2(xr[n1], xi[n1]);
+                }
+                slot_bar(slot);
+                {
+                    const double2 *__restrict__ Sw = ss.S[w];
+#pragma unroll
+                    for (int k2 = 0; k2 < 32; k2++) {
+                        const double2 v = Sw[k2 * kTStride + lane];
+                        xr[FHS_BR5(k2)] = v.x;
+                        xi[FHS_BR5(k2)] = v.y;
+                    }
+                }
+                fft32_neg(xr, xi);
+                // ---- conjugate pre-twist, add as torus into the TMEM accumulator ----
+#pragma unroll
+                for (int c = 0; c < 4; c++) {   // 8 values of m (16 coefficients) per chunk
+                    uint32_t ohi[16], olo[16];
+                    tmem_ld16(tacc + 16 * c, ohi);
+                    tmem_ld16(tacc + 64 + 16 * c, olo);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int mm = 0; mm < 8; mm++) {
+                        const int m = 8 * c + mm;
+                        double ur, ui;
+                        if (m == 0) {
+                            ur = xr[m];
+                            ui = xi[m];
+                        } else {
+                            ur = xr[m] * kPreRe[m] + xi[m] * kPreIm[m];
+                            ui = xi[m] * kPreRe[m] - xr[m] * kPreIm[m];
+                        }
+                        const uint64_t n0 = (((uint64_t)ohi[2 * mm] << 32) | olo[2 * mm]) + f64_to_torus(ur);
+                        const uint64_t n1v = (((uint64_t)ohi[2 * mm + 1] << 32) | olo[2 * mm + 1]) + f64_to_torus(ui);
+                        ohi[2 * mm] = (uint32_t)(n0 >> 32);
+                        olo[2 * mm] = (uint32_t)n0;
+                        ohi[2 * mm + 1] = (uint32_t)(n1v >> 32);
+                        olo[2 * mm + 1] = (uint32_t)n1v;
+                        H[lane + 32 * m] = ohi[2 * mm];
+                        H[lane + 32 * m + kH] = ohi[2 * mm + 1];
+                    }
+                    tmem_st16(tacc + 16 * c, ohi);
+                    tmem_st16(tacc + 64 + 16 * c, olo);
+                }
+                tmem_wait_st();
+                __syncwarp();  // hi plane of polynomial w complete before this warp's rotated reads
+            }
+
+            // ---- a1.7 sample extract at coefficient 0, from the TMEM accumulator ----
+            {
+                uint32_t vhi[64], vlo[64];
+                tmem_ld64(tacc, vhi);
+                tmem_ld64(tacc + 64, vlo);
+                tmem_wait_ld();
+                uint64_t *__restrict__ out = lwe_out + (size_t)ct * (kN + 1);
+                if (w == 0) {
+                    // out[0] = A[0]; out[j] = -A[N - j]  <=>  coefficient c goes to out[(N - c) % N]
+#pragma unroll
+                    for (int q = 0; q < 64; q++) {
+                        const int cidx = lane + 32 * (q >> 1) + kH * (q & 1);
+                        const uint64_t v = ((uint64_t)vhi[q] << 32) | vlo[q];
+                        if (cidx == 0) out[0] = v;
+                        else out[kN - cidx] = 0ull - v;
+                    }
+                } else if (lane == 0) {
+                    out[kN] = ((uint64_t)vhi[0] << 32) | vlo[0];
+                }
+            }
+            slot_bar(slot);  // amod / hi plane reuse by the next group
+        }
+    }
+    tmem_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(sm.tmem_base, kTmemCols);
+}
+
 // Forward transform of the standard-domain BSK into the layout the kernel above reads:
 //   bsk_f[(((i*32 + k1)*2 + w)*32 + lane)*2 + slot],  rp = lane >> 4, k2 = 16 w + (lane & 15),
 //   slot 0 = GGSW row rp, column 1-rp ("send"), slot 1 = row rp, column rp ("keep"),
@@ -387,21 +704,33 @@ int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc) {
 int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                         const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static int variant = -1;
+    if (variant < 0) {
+        const char *e = getenv("FHS_BR_VARIANT");
+        variant = e ? atoi(e) : 2;
         FHS_CUDA(cudaFuncSetAttribute(blind_rotate_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(Smem)));
-        attr_set = true;
+        FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(Smem2)));
     }
     const int log_box = ilog2(kN / c->space);
     const uint64_t delta = (1ull << 63) / c->space;
-    FHS_CUDA(cudaMemsetAsync(c->d_counter, 0, sizeof(unsigned int), c->stream));
-    size_t ctas = (batch + kCtPerCta - 1) / kCtPerCta;
-    if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
-    blind_rotate_kernel<<<(unsigned)ctas, kThreads, sizeof(Smem), c->stream>>>(
-        d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, c->d_counter,
-        (unsigned int)batch, (int)c->n, log_box, delta);
+    if (variant == 1) {
+        FHS_CUDA(cudaMemsetAsync(c->d_counter, 0, sizeof(unsigned int), c->stream));
+        size_t ctas = (batch + kCtPerCta - 1) / kCtPerCta;
+        if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
+        blind_rotate_kernel<<<(unsigned)ctas, kThreads, sizeof(Smem), c->stream>>>(
+            d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, c->d_counter,
+            (unsigned int)batch, (int)c->n, log_box, delta);
+    } else {
+        size_t ctas = (batch + kSlots2 - 1) / kSlots2;
+        if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
+        blind_rotate_v2_kernel<<<(unsigned)ctas, kThreads2, sizeof(Smem2), c->stream>>>(
+            d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, (unsigned int)batch,
+            (int)c->n, log_box, delta);
+    }
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     return FHS_OK;

@@ -73,9 +73,8 @@ def test_blind_rotate_close_to_oracle(engine, keyset):
     got = engine.pbs(small, lut_id, tables)
     want = keyset.ks_pbs_batch(cts, lut_id, tables)
     assert np.array_equal(keyset.decrypt(got), keyset.decrypt(want))
-    d = (got - want).astype(np.int64).astype(np.float64) / 2.0**64
-    # coefficient-wise distance of the two LWE ciphertexts: both carry independent rounding noise
-    assert np.abs(d).max() < 2.0**-10
+    # The ciphertexts are NOT coefficient-wise close: FFT rounding flips some signed digits, and one
+    # flipped digit adds a whole (uniformly random) GGSW row.  What must agree is the phase.
     ph = keyset.phase_error(got, tables[lut_id, msgs]) - keyset.phase_error(want, tables[lut_id, msgs])
     assert np.std(ph) < 6e-5
 
