@@ -339,9 +339,11 @@ __device__ __forceinline__ void named_bar_arrive(int id, int n) {
     asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
 }
 
+// Signed digit (base 2^23, one level) from the high word of the value: round(x / 2^41) as a
+// signed 23-bit integer.  Equals the tfhe rule except at the single tie x/2^41 = 2^22 - 1/2, where
+// it returns -2^22 instead of +2^22 (the same value mod 2^64).
 __device__ __forceinline__ int pbs_digit_hi(uint32_t hi) {
-    const uint32_t s = (((hi >> 8) + 1u) >> 1) & 0x7FFFFFu;
-    return (int)s - (int)((s > 0x400000u) ? 0x800000u : 0u);
+    return (int)(hi + 0x100u) >> 9;
 }
 
 __device__ __forceinline__ void ldg_b128(const void *p, uint32_t &a, uint32_t &b, uint32_t &c,
@@ -454,16 +456,17 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         const uint32_t idx1 = (idx0 + kH) & (2 * kN - 1);
                         uint32_t r0 = H[idx0 & (kN - 1)];
                         uint32_t r1 = H[idx1 & (kN - 1)];
-                        r0 = (idx0 & kN) ? ~r0 : r0;
-                        r1 = (idx1 & kN) ? ~r1 : r1;
-                        const double d0 = int_to_double(pbs_digit_hi(r0 - own[2 * m]));
-                        const double d1 = int_to_double(pbs_digit_hi(r1 - own[2 * m + 1]));
+                        // negacyclic wrap: -x on the high word is ~x up to the dropped borrow
+                        r0 ^= (uint32_t)((int)(idx0 << 20) >> 31);
+                        r1 ^= (uint32_t)((int)(idx1 << 20) >> 31);
+                        const double d0 = __int2double_rn(pbs_digit_hi(r0 - own[2 * m]));
+                        const double d1 = __int2double_rn(pbs_digit_hi(r1 - own[2 * m + 1]));
                         if (m == 0) {
                             xr[FHS_BR5(m)] = d0;
                             xi[FHS_BR5(m)] = d1;
                         } else {
-                            xr[FHS_BR5(m)] = d0 * kPreRe[m] - d1 * kPreIm[m];
-                            xi[FHS_BR5(m)] = d0 * kPreIm[m] + d1 * kPreRe[m];
+                            xr[FHS_BR5(m)] = d0 * fhs_pre_re(m) - d1 * fhs_pre_im(m);
+                            xi[FHS_BR5(m)] = d0 * fhs_pre_im(m) + d1 * fhs_pre_re(m);
                         }
                     }
                 }
@@ -563,8 +566,8 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                             ur = xr[m];
                             ui = xi[m];
                         } else {
-                            ur = xr[m] * kPreRe[m] + xi[m] * kPreIm[m];
-                            ui = xi[m] * kPreRe[m] - xr[m] * kPreIm[m];
+                            ur = xr[m] * fhs_pre_re(m) + xi[m] * fhs_pre_im(m);
+                            ui = xi[m] * fhs_pre_re(m) - xr[m] * fhs_pre_im(m);
                         }
                         const uint64_t n0 = (((uint64_t)ohi[2 * mm] << 32) | olo[2 * mm]) + f64_to_torus(ur);
                         const uint64_t n1v = (((uint64_t)ohi[2 * mm + 1] << 32) | olo[2 * mm + 1]) + f64_to_torus(ui);
