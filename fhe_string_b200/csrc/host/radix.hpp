@@ -1,0 +1,296 @@
+// Radix-integer and boolean primitives as level programs (replaces the tfhe::integer::ServerKey
+// methods fhe_string calls: SURVEY.md 2.2 -- boolean_bitand/or/not, scalar_eq/ne/gt/ge/le,
+// eq/lt/ge, if_then_else, add/sub/scalar_add, sum of selected values, ...).  The algorithms are
+// free (only decrypted results must match); these are chosen for low depth and
+// few LUT evaluations at message_modulus = carry_modulus = 4:
+//   * two clean blocks pack into one 4-bit value 4*hi+lo;
+//   * two packed values are compared with ONE signed PBS on their difference (padding bit /
+//     negacyclic trick, SURVEY.md 7 "negacyclic semantics are relied upon");
+//   * selections use 4*cond + block <= 7 in one PBS per block.
+#pragma once
+#include <algorithm>
+#include <functional>
+
+#include "graph.hpp"
+
+namespace fhs_host {
+
+using Bool = Lin;                // value in {0,1}
+using Rad = std::vector<Lin>;    // little-endian base-4 digits, each in [0,3]
+
+struct Ops {
+    Graph &g;
+    explicit Ops(Graph &g_) : g(g_) {}
+
+    // ---------------- booleans ----------------
+    Bool band(const Bool &a, const Bool &b) {
+        return g.pbs(add(a, b), [](int x) { return x == 2; }, 0, 1);
+    }
+    Bool bor(const Bool &a, const Bool &b) {
+        return g.pbs(add(a, b), [](int x) { return x >= 1; }, 0, 1);
+    }
+    // AND / OR of any number of booleans: sums of <= 15 terms, one PBS per chunk, log depth.
+    Bool all(std::vector<Bool> v) {
+        if (v.empty()) return Graph::constant(1);
+        while (v.size() > 1) {
+            std::vector<Bool> nx;
+            for (size_t i = 0; i < v.size(); i += 15) {
+                size_t n = std::min<size_t>(15, v.size() - i);
+                Lin s = Graph::constant(0);
+                for (size_t j = 0; j < n; j++) s = add(s, v[i + j]);
+                int nn = (int)n;
+                nx.push_back(n == 1 ? v[i] : g.pbs(s, [nn](int x) { return x == nn; }, 0, 1));
+            }
+            v.swap(nx);
+        }
+        return v[0];
+    }
+    Bool any(std::vector<Bool> v) {
+        if (v.empty()) return Graph::constant(0);
+        while (v.size() > 1) {
+            std::vector<Bool> nx;
+            for (size_t i = 0; i < v.size(); i += 15) {
+                size_t n = std::min<size_t>(15, v.size() - i);
+                Lin s = Graph::constant(0);
+                for (size_t j = 0; j < n; j++) s = add(s, v[i + j]);
+                nx.push_back(n == 1 ? v[i] : g.pbs(s, [](int x) { return x >= 1; }, 0, 1));
+            }
+            v.swap(nx);
+        }
+        return v[0];
+    }
+    // Inclusive prefix OR: p[i] = v[0] | ... | v[i]; two/three-level blocked scan (chunks of 15).
+    std::vector<Bool> prefix_or(const std::vector<Bool> &v) {
+        const size_t n = v.size();
+        std::vector<Bool> p(n);
+        if (n == 0) return p;
+        const size_t C = 14;  // 14 bools + 1 carry <= 15
+        const size_t nch = (n + C - 1) / C;
+        std::vector<Bool> tot(nch);
+        std::vector<Lin> run(n);
+        for (size_t ch = 0; ch < nch; ch++) {
+            Lin s = Graph::constant(0);
+            for (size_t i = ch * C; i < std::min(n, (ch + 1) * C); i++) { s = add(s, v[i]); run[i] = s; }
+            tot[ch] = s;  // raw sum (<= 15)
+        }
+        std::vector<Bool> carry;  // OR of all chunks strictly before ch
+        if (nch > 1) {
+            std::vector<Bool> tb(nch - 1);
+            for (size_t ch = 0; ch + 1 < nch; ch++) tb[ch] = g.pbs(tot[ch], [](int x) { return x >= 1; }, 0, 1);
+            std::vector<Bool> pc = prefix_or(tb);
+            carry.push_back(Graph::constant(0));
+            for (size_t ch = 0; ch + 1 < nch; ch++) carry.push_back(pc[ch]);
+        } else {
+            carry.push_back(Graph::constant(0));
+        }
+        for (size_t i = 0; i < n; i++) {
+            Lin s = add(run[i], carry[i / C]);
+            p[i] = g.pbs(s, [](int x) { return x >= 1; }, 0, 1);
+        }
+        return p;
+    }
+
+    // ---------------- packing ----------------
+    // pairs of clean blocks -> 4-bit values (last one may be a single block)
+    std::vector<Lin> pack(const Rad &a) {
+        std::vector<Lin> p;
+        for (size_t i = 0; i < a.size(); i += 2)
+            p.push_back(i + 1 < a.size() ? add(a[i], scale(a[i + 1], 4)) : a[i]);
+        return p;
+    }
+    static std::vector<int> pack_scalar(uint64_t c, size_t nblocks) {
+        std::vector<int> p;
+        for (size_t i = 0; i < nblocks; i += 2) {
+            int lo = (int)((c >> (2 * i)) & 3), hi = (i + 1 < nblocks) ? (int)((c >> (2 * i + 2)) & 3) : 0;
+            p.push_back(lo + 4 * hi);
+        }
+        return p;
+    }
+    static bool scalar_fits(uint64_t c, size_t nblocks) { return nblocks >= 32 || (c >> (2 * nblocks)) == 0; }
+
+    // ---------------- equality ----------------
+    std::vector<Bool> eq_bits(const Rad &a, const Rad &b) {  // one bool per packed pair
+        std::vector<Lin> pa = pack(a), pb = pack(b);
+        std::vector<Bool> r;
+        for (size_t i = 0; i < pa.size(); i++)
+            r.push_back(g.pbs(sub(pa[i], pb[i]), [](int x) { return x == 0; }, 0, 1, true));
+        return r;
+    }
+    Bool eq(const Rad &a, const Rad &b) { return all(eq_bits(a, b)); }
+    std::vector<Bool> eq_scalar_bits(const Rad &a, uint64_t c) {
+        std::vector<Lin> pa = pack(a);
+        std::vector<int> pc = pack_scalar(c, a.size());
+        std::vector<Bool> r;
+        for (size_t i = 0; i < pa.size(); i++) {
+            int ci = pc[i];
+            r.push_back(g.pbs(pa[i], [ci](int x) { return x == ci; }, 0, 1));
+        }
+        return r;
+    }
+    Bool eq_scalar(const Rad &a, uint64_t c) {
+        if (!scalar_fits(c, a.size())) return Graph::constant(0);
+        return all(eq_scalar_bits(a, c));
+    }
+    // a == 0 for a radix of <= 5 clean blocks: one PBS on the digit sum
+    Bool is_zero(const Rad &a) {
+        std::vector<Bool> parts;
+        for (size_t i = 0; i < a.size(); i += 5) {
+            Lin s = Graph::constant(0);
+            for (size_t j = i; j < std::min(a.size(), i + 5); j++) s = add(s, a[j]);
+            parts.push_back(g.pbs(s, [](int x) { return x == 0; }, 0, 1));
+        }
+        return all(parts);
+    }
+
+    // ---------------- ordering ----------------
+    // sign in {0: a<b, 1: a==b, 2: a>b} per packed pair, most significant pair last
+    std::vector<Lin> sign_pairs(const std::vector<Lin> &pa, const std::vector<Lin> &pb) {
+        std::vector<Lin> s;
+        for (size_t i = 0; i < pa.size(); i++) {
+            Lin d = g.pbs(sub(pa[i], pb[i]), [](int x) { return x == 0 ? 0 : 1; }, -1, 1, true);
+            s.push_back(bounded(addc(d, 1), 0, 2));
+        }
+        return s;
+    }
+    // reduce signs (index 0 least significant) to one sign, then map through `fin`
+    Bool reduce_sign(std::vector<Lin> s, std::function<int(int)> fin) {
+        if (s.empty()) return Graph::constant(fin(1));
+        while (s.size() > 1) {
+            std::vector<Lin> nx;
+            size_t i = 0;
+            for (; i + 1 < s.size(); i += 2) {
+                Lin x = add(scale(s[i + 1], 3), s[i]);  // hi*3 + lo <= 8
+                if (s.size() == 2) {
+                    return g.pbs(x, [fin](int v) { int hi = v / 3, lo = v % 3; return fin(hi == 1 ? lo : hi); }, 0, 1);
+                }
+                nx.push_back(g.pbs(x, [](int v) { int hi = v / 3, lo = v % 3; return hi == 1 ? lo : hi; }, 0, 2));
+            }
+            if (i < s.size()) nx.push_back(s[i]);
+            s.swap(nx);
+        }
+        return g.pbs(s[0], [fin](int v) { return fin(v); }, 0, 1);
+    }
+    // generic comparison with final map fin(sign)
+    Bool cmp(const Rad &a, const Rad &b, std::function<int(int)> fin) {
+        return reduce_sign(sign_pairs(pack(a), pack(b)), fin);
+    }
+    Bool cmp_scalar(const Rad &a, uint64_t c, std::function<int(int)> fin) {
+        if (!scalar_fits(c, a.size())) return Graph::constant(fin(0));  // a < c always
+        std::vector<int> pc = pack_scalar(c, a.size());
+        std::vector<Lin> pb;
+        for (int v : pc) pb.push_back(Graph::constant(v));
+        return reduce_sign(sign_pairs(pack(a), pb), fin);
+    }
+    Bool lt(const Rad &a, const Rad &b) { return cmp(a, b, [](int s) { return s == 0; }); }
+    Bool le(const Rad &a, const Rad &b) { return cmp(a, b, [](int s) { return s <= 1; }); }
+    Bool gt(const Rad &a, const Rad &b) { return cmp(a, b, [](int s) { return s == 2; }); }
+    Bool ge(const Rad &a, const Rad &b) { return cmp(a, b, [](int s) { return s >= 1; }); }
+    Bool lt_scalar(const Rad &a, uint64_t c) { return cmp_scalar(a, c, [](int s) { return s == 0; }); }
+    Bool gt_scalar(const Rad &a, uint64_t c) { return cmp_scalar(a, c, [](int s) { return s == 2; }); }
+
+    // ---------------- selection ----------------
+    // c ? a : 0   (logic.rs:13 if_then_else_zero -- one PBS per block instead of a radix multiply)
+    Rad select_zero(const Bool &c, const Rad &a) {
+        Rad r;
+        for (auto &blk : a)
+            r.push_back(g.pbs(add(scale(c, 4), blk), [](int x) { return x >= 4 ? (x & 3) : 0; }, 0, 3));
+        return r;
+    }
+    Rad if_then_else(const Bool &c, const Rad &a, const Rad &b) {
+        Rad r;
+        for (size_t i = 0; i < a.size(); i++) {
+            Lin t = g.pbs(add(scale(c, 4), a[i]), [](int x) { return x >= 4 ? (x & 3) : 0; }, 0, 3);
+            Lin f = g.pbs(add(scale(c, 4), b[i]), [](int x) { return x < 4 ? x : 0; }, 0, 3);
+            r.push_back(bounded(add(t, f), 0, 3));
+        }
+        return r;
+    }
+    Bool if_then_else_bool(const Bool &c, const Bool &a, const Bool &b) {
+        // 4c + 2a + b <= 7
+        return g.pbs(add(add(scale(c, 4), scale(a, 2)), b), [](int x) { return x >= 4 ? ((x >> 1) & 1) : (x & 1); }, 0, 1);
+    }
+    // c ? scalar : 0 (logic.rs:19 scalar_if_then_else_zero): linear, no PBS
+    Rad bool_times_scalar(const Bool &c, uint64_t v, size_t nblocks) {
+        Rad r;
+        for (size_t i = 0; i < nblocks; i++) r.push_back(bounded(scale(c, (int)((v >> (2 * i)) & 3)), 0, (int)((v >> (2 * i)) & 3)));
+        return r;
+    }
+    static Rad scalar(uint64_t v, size_t nblocks) {
+        Rad r;
+        for (size_t i = 0; i < nblocks; i++) r.push_back(Graph::constant((int64_t)((v >> (2 * i)) & 3)));
+        return r;
+    }
+    Rad from_bool(const Bool &b, size_t nblocks) {
+        Rad r{b};
+        for (size_t i = 1; i < nblocks; i++) r.push_back(Graph::constant(0));
+        return r;
+    }
+    // Sum of radix values of which AT MOST ONE is non-zero (one-hot selections): linear, with an
+    // identity-LUT refresh every 48 addends to bound the noise of the running sum.
+    Rad onehot_sum(const std::vector<Rad> &v, size_t nblocks) {
+        Rad acc = scalar(0, nblocks);
+        size_t pending = 0;
+        for (auto &r : v) {
+            for (size_t i = 0; i < nblocks; i++) acc[i] = bounded(add(acc[i], r[i]), 0, 3);
+            if (++pending == 48) {
+                for (size_t i = 0; i < nblocks; i++)
+                    acc[i] = g.pbs(acc[i], [](int x) { return x & 3; }, 0, 3);
+                pending = 1;
+            }
+        }
+        return acc;
+    }
+
+    // ---------------- addition ----------------
+    // blocks s_i in [0,7] (digit sums incl. injected +1) -> clean digits of the sum mod 4^n
+    Rad propagate(const std::vector<Lin> &s) {
+        const size_t n = s.size();
+        if (n == 0) return {};
+        // carry state per block: 0 none, 1 propagate (s==3), 2 generate (s>=4)
+        std::vector<Lin> st(n);
+        for (size_t i = 0; i + 1 < n; i++)
+            st[i] = s[i].is_const() ? Graph::constant(s[i].c >= 4 ? 2 : (s[i].c == 3 ? 1 : 0))
+                                    : g.pbs(s[i], [](int x) { return x >= 4 ? 2 : (x == 3 ? 1 : 0); }, 0, 2);
+        // inclusive prefix of the carry operator (Hillis-Steele): pre[i] = state of blocks 0..i
+        std::vector<Lin> pre(st.begin(), st.begin() + (n ? n - 1 : 0));
+        for (size_t d = 1; d < pre.size(); d *= 2) {
+            std::vector<Lin> nx = pre;
+            for (size_t i = d; i < pre.size(); i++)
+                nx[i] = g.pbs(add(scale(pre[i], 3), pre[i - d]),
+                              [](int v) { int hi = v / 3, lo = v % 3; return hi == 1 ? lo : hi; }, 0, 2);
+            pre.swap(nx);
+        }
+        Rad out(n);
+        for (size_t i = 0; i < n; i++) {
+            if (i == 0) { out[i] = g.pbs(s[i], [](int x) { return x & 3; }, 0, 3); continue; }
+            // carry-in = (pre[i-1] == 2); s_i + 8*... does not fit: fold carry via 2-step value
+            Lin cin = g.pbs(pre[i - 1], [](int v) { return v == 2; }, 0, 1);
+            out[i] = g.pbs(bounded(add(s[i], cin), 0, 8), [](int x) { return x & 3; }, 0, 3);
+        }
+        return out;
+    }
+    Rad add_rad(const Rad &a, const Rad &b) {
+        std::vector<Lin> s;
+        for (size_t i = 0; i < a.size(); i++) s.push_back(add(a[i], b[i]));
+        return propagate(s);
+    }
+    Rad add_scalar(const Rad &a, uint64_t c) {
+        std::vector<Lin> s;
+        for (size_t i = 0; i < a.size(); i++) s.push_back(addc(a[i], (int64_t)((c >> (2 * i)) & 3)));
+        return propagate(s);
+    }
+    Rad sub_rad(const Rad &a, const Rad &b) {  // a - b mod 4^n = a + ~b + 1
+        std::vector<Lin> s;
+        for (size_t i = 0; i < a.size(); i++) {
+            Lin x = bounded(add(a[i], sub(Graph::constant(3), b[i])), 0, 6);
+            if (i == 0) x = bounded(addc(x, 1), 0, 7);
+            s.push_back(x);
+        }
+        return propagate(s);
+    }
+    // low bit / high bit of a clean block
+    Bool bit0(const Lin &blk) { return g.pbs(blk, [](int x) { return x & 1; }, 0, 1); }
+    Bool bit1(const Lin &blk) { return g.pbs(blk, [](int x) { return (x >> 1) & 1; }, 0, 1); }
+};
+
+}  // namespace fhs_host

@@ -1,0 +1,169 @@
+// Device-resident ciphertext pool and level execution (SURVEY.md 8b "device-resident variant"):
+//   K1 gather + linear-combination prologue:  in[b] = sum_t coef[b][t] * pool[idx[b][t]] + const[b]
+//   (bivariate pack 4x+y, compare x-y, block pack 4hi+lo, <=5-term sums, scalar add; replaces the
+//   linear shortint ops tfhe-rs runs before each PBS: unchecked_scalar_mul / unchecked_add / sub),
+//   then keyswitch + blind rotation of the whole level, results written to consecutive pool slots.
+#include "fhs_internal.cuh"
+
+namespace fhs {
+
+struct Pool {
+    Ctx *ctx;
+    uint64_t *d = nullptr;
+    size_t capacity = 0;
+    // level descriptor staging (device)
+    uint32_t *d_off = nullptr, *d_idx = nullptr, *d_lut = nullptr;
+    int32_t *d_coef = nullptr;
+    uint64_t *d_cst = nullptr, *d_tables = nullptr;
+    size_t cap_b = 0, cap_t = 0, cap_luts = 0;
+    uint64_t *d_stage = nullptr;  // [cap_b][big+1] linear-combination results
+};
+
+namespace {
+
+__global__ void __launch_bounds__(256)
+gather_linear_kernel(const uint64_t *__restrict__ pool, const uint32_t *__restrict__ off,
+                     const uint32_t *__restrict__ idx, const int32_t *__restrict__ coef,
+                     const uint64_t *__restrict__ cst, uint64_t *__restrict__ out, int width) {
+    const unsigned b = blockIdx.x;
+    const uint32_t t0 = off[b], t1 = off[b + 1];
+    uint64_t *__restrict__ o = out + (size_t)b * width;
+    for (int j = threadIdx.x; j < width; j += blockDim.x) {
+        uint64_t acc = (j == width - 1) ? cst[b] : 0ull;
+        for (uint32_t t = t0; t < t1; t++)
+            acc += (uint64_t)(int64_t)coef[t] * pool[(size_t)idx[t] * width + j];
+        o[j] = acc;
+    }
+}
+
+int ensure_desc(Pool *p, size_t B, size_t T, size_t n_luts) {
+    Ctx *c = p->ctx;
+    if (B > p->cap_b) {
+        size_t cap = p->cap_b ? p->cap_b : 1024;
+        while (cap < B) cap *= 2;
+        cudaFree(p->d_off); cudaFree(p->d_lut); cudaFree(p->d_cst); cudaFree(p->d_stage);
+        p->d_off = p->d_lut = nullptr; p->d_cst = nullptr; p->d_stage = nullptr; p->cap_b = 0;
+        FHS_CUDA(cudaMalloc(&p->d_off, (cap + 1) * sizeof(uint32_t)));
+        FHS_CUDA(cudaMalloc(&p->d_lut, cap * sizeof(uint32_t)));
+        FHS_CUDA(cudaMalloc(&p->d_cst, cap * sizeof(uint64_t)));
+        FHS_CUDA(cudaMalloc(&p->d_stage, cap * ((size_t)c->big + 1) * sizeof(uint64_t)));
+        p->cap_b = cap;
+    }
+    if (T > p->cap_t) {
+        size_t cap = p->cap_t ? p->cap_t : 4096;
+        while (cap < T) cap *= 2;
+        cudaFree(p->d_idx); cudaFree(p->d_coef);
+        p->d_idx = nullptr; p->d_coef = nullptr; p->cap_t = 0;
+        FHS_CUDA(cudaMalloc(&p->d_idx, cap * sizeof(uint32_t)));
+        FHS_CUDA(cudaMalloc(&p->d_coef, cap * sizeof(int32_t)));
+        p->cap_t = cap;
+    }
+    if (n_luts > p->cap_luts) {
+        size_t cap = p->cap_luts ? p->cap_luts : 64;
+        while (cap < n_luts) cap *= 2;
+        cudaFree(p->d_tables);
+        p->d_tables = nullptr; p->cap_luts = 0;
+        FHS_CUDA(cudaMalloc(&p->d_tables, cap * c->space * sizeof(uint64_t)));
+        p->cap_luts = cap;
+    }
+    return FHS_OK;
+}
+
+}  // namespace
+}  // namespace fhs
+
+using fhs::Ctx;
+using fhs::Pool;
+
+extern "C" {
+
+int fhs_pool_create(fhs_ctx *h, size_t capacity_blocks, fhs_pool **out) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !out || capacity_blocks == 0) return FHS_ERR_INVALID;
+    if (!c->has_keys) { fhs::set_error("keys not uploaded"); return FHS_ERR_NO_KEYS; }
+    FHS_CUDA(cudaSetDevice(c->device));
+    Pool *p = new Pool();
+    p->ctx = c;
+    cudaError_t e = cudaMalloc(&p->d, capacity_blocks * ((size_t)c->big + 1) * sizeof(uint64_t));
+    if (e != cudaSuccess) { delete p; return fhs::cuda_fail(e, "cudaMalloc(pool)"); }
+    p->capacity = capacity_blocks;
+    *out = reinterpret_cast<fhs_pool *>(p);
+    return FHS_OK;
+}
+
+void fhs_pool_destroy(fhs_pool *hp) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p) return;
+    cudaSetDevice(p->ctx->device);
+    cudaStreamSynchronize(p->ctx->stream);
+    cudaFree(p->d); cudaFree(p->d_off); cudaFree(p->d_idx); cudaFree(p->d_lut); cudaFree(p->d_coef);
+    cudaFree(p->d_cst); cudaFree(p->d_tables); cudaFree(p->d_stage);
+    delete p;
+}
+
+size_t fhs_pool_capacity(fhs_pool *hp) { return hp ? reinterpret_cast<Pool *>(hp)->capacity : 0; }
+uint64_t *fhs_pool_device_ptr(fhs_pool *hp) { return hp ? reinterpret_cast<Pool *>(hp)->d : nullptr; }
+
+int fhs_pool_write(fhs_pool *hp, size_t slot, size_t n, const uint64_t *host_blocks) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || (!host_blocks && n) || slot + n > p->capacity) { fhs::set_error("pool write out of range"); return FHS_ERR_INVALID; }
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    const size_t w = (size_t)c->big + 1;
+    FHS_CUDA(cudaMemcpyAsync(p->d + slot * w, host_blocks, n * w * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+    FHS_CUDA(cudaStreamSynchronize(c->stream));
+    return FHS_OK;
+}
+
+int fhs_pool_read(fhs_pool *hp, size_t slot, size_t n, uint64_t *host_blocks) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || (!host_blocks && n) || slot + n > p->capacity) { fhs::set_error("pool read out of range"); return FHS_ERR_INVALID; }
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    const size_t w = (size_t)c->big + 1;
+    FHS_CUDA(cudaMemcpyAsync(host_blocks, p->d + slot * w, n * w * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+    FHS_CUDA(cudaStreamSynchronize(c->stream));
+    return FHS_OK;
+}
+
+// One level: B linear combinations of pool blocks; if lut_id != NULL each is keyswitched and
+// bootstrapped through lut_tables[lut_id[b]]; results land in pool slots [out_slot, out_slot + B).
+int fhs_level(fhs_pool *hp, size_t B, const uint32_t *term_off, const uint32_t *term_idx,
+              const int32_t *term_coef, const uint64_t *const_body, const uint32_t *lut_id,
+              const uint64_t *lut_tables, size_t n_luts, size_t out_slot) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p) return FHS_ERR_INVALID;
+    if (B == 0) return FHS_OK;
+    Ctx *c = p->ctx;
+    if (!term_off || !const_body || out_slot + B > p->capacity || (lut_id && (!lut_tables || !n_luts))) {
+        fhs::set_error("fhs_level: bad arguments (out_slot %zu + B %zu vs capacity %zu)", out_slot, B, p->capacity);
+        return FHS_ERR_INVALID;
+    }
+    const size_t T = term_off[B];
+    FHS_CUDA(cudaSetDevice(c->device));
+    int rc = fhs::ensure_desc(p, B, T, lut_id ? n_luts : 0);
+    if (rc != FHS_OK) return rc;
+    cudaStream_t s = c->stream;
+    FHS_CUDA(cudaMemcpyAsync(p->d_off, term_off, (B + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+    if (T) {
+        FHS_CUDA(cudaMemcpyAsync(p->d_idx, term_idx, T * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+        FHS_CUDA(cudaMemcpyAsync(p->d_coef, term_coef, T * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    }
+    FHS_CUDA(cudaMemcpyAsync(p->d_cst, const_body, B * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
+    const int width = (int)c->big + 1;
+    uint64_t *dst = p->d + out_slot * (size_t)width;
+    if (!lut_id) {
+        fhs::gather_linear_kernel<<<(unsigned)B, 256, 0, s>>>(p->d, p->d_off, p->d_idx, p->d_coef, p->d_cst, dst, width);
+        c->launches++;
+        FHS_CUDA(cudaGetLastError());
+        return FHS_OK;
+    }
+    FHS_CUDA(cudaMemcpyAsync(p->d_lut, lut_id, B * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+    FHS_CUDA(cudaMemcpyAsync(p->d_tables, lut_tables, n_luts * c->space * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
+    fhs::gather_linear_kernel<<<(unsigned)B, 256, 0, s>>>(p->d, p->d_off, p->d_idx, p->d_coef, p->d_cst, p->d_stage, width);
+    c->launches++;
+    FHS_CUDA(cudaGetLastError());
+    return fhs_ks_pbs_batch_dev(reinterpret_cast<fhs_ctx *>(c), p->d_stage, p->d_lut, p->d_tables, n_luts, B, dst);
+}
+
+}  // extern "C"

@@ -113,6 +113,26 @@ uint64_t fhs_launch_count(fhs_ctx *ctx);
  * of 4 after a warm-up): the roofline denominator of the blind-rotation kernel. */
 int fhs_measure_fp64_tflops(fhs_ctx *ctx, double *tflops_out);
 
+/* ---- device-resident ciphertext pool + level execution ------------------------
+ * A pool is a device array of big-key LWE blocks [capacity][k*N+1].  fhs_level evaluates one level
+ * of a radix/string operation: for b < B
+ *     in_b = sum_{t in [term_off[b], term_off[b+1])} term_coef[t] * pool[term_idx[t]]  + (0,..,0,const_body[b])
+ *     pool[out_slot + b] = lut_id ? KS-PBS(in_b, lut_tables[lut_id[b]]) : in_b
+ * (const_body is already scaled by Delta).  Replaces the linear shortint ops + apply_lookup_table
+ * sequences tfhe-rs runs per block (unchecked_scalar_mul/add/sub + keyswitch_programmable_bootstrap).
+ * Descriptor arrays are host pointers; ciphertexts never leave the GPU.  Asynchronous on the
+ * context's stream; fhs_pool_read synchronises. */
+typedef struct fhs_pool fhs_pool;
+int fhs_pool_create(fhs_ctx *ctx, size_t capacity_blocks, fhs_pool **out);
+void fhs_pool_destroy(fhs_pool *pool);
+size_t fhs_pool_capacity(fhs_pool *pool);
+uint64_t *fhs_pool_device_ptr(fhs_pool *pool);
+int fhs_pool_write(fhs_pool *pool, size_t slot, size_t n, const uint64_t *host_blocks);
+int fhs_pool_read(fhs_pool *pool, size_t slot, size_t n, uint64_t *host_blocks);
+int fhs_level(fhs_pool *pool, size_t B, const uint32_t *term_off, const uint32_t *term_idx,
+              const int32_t *term_coef, const uint64_t *const_body, const uint32_t *lut_id,
+              const uint64_t *lut_tables, size_t n_luts, size_t out_slot);
+
 #ifdef __cplusplus
 }
 #endif
