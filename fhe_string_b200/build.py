@@ -44,7 +44,23 @@ def build(force=False, verbose=False):
     if force or _stale(LIB, objs):
         subprocess.check_call([nvcc, "-shared", "-o", LIB] + objs + ["-gencode",
                               "arch=compute_100a,code=sm_100a"])
+    build_host(force)
     return LIB
+
+
+HOST_LIB = os.path.join(HERE, "libfhs_string.so")
+
+
+def build_host(force=False):
+    """g++: host-side level scheduler (include/fhs_string.h), linked against libfhs_cuda.so."""
+    hdir = os.path.join(CSRC, "host")
+    srcs = [os.path.join(hdir, f) for f in sorted(os.listdir(hdir)) if f.endswith(".cpp")]
+    deps = [os.path.join(hdir, f) for f in os.listdir(hdir)] + [
+        os.path.join(HERE, "..", "include", "fhs_string.h"), os.path.join(HERE, "..", "include", "fhs_cuda.h"), LIB]
+    if force or _stale(HOST_LIB, deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-o", HOST_LIB] + srcs +
+                              ["-L" + HERE, "-lfhs_cuda", "-Wl,-rpath,$ORIGIN"])
+    return HOST_LIB
 
 
 if __name__ == "__main__":

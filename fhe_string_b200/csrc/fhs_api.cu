@@ -166,6 +166,17 @@ int fhs_ctx_synchronize(fhs_ctx *h) {
     return FHS_OK;
 }
 
+int fhs_ctx_get_params(fhs_ctx *h, fhs_params *out) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !out) return FHS_ERR_INVALID;
+    if (!c->has_keys) {
+        fhs::set_error("keys not uploaded");
+        return FHS_ERR_NO_KEYS;
+    }
+    *out = c->p;
+    return FHS_OK;
+}
+
 int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
                     const uint64_t *bsk) {
     if (!h || !p || !ksk || !bsk) {

@@ -1,0 +1,248 @@
+// fhs_prog: build / export / run level programs (include/fhs_string.h).
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../../include/fhs_string.h"
+#include "strings.hpp"
+
+using namespace fhs_host;
+
+struct fhs_prog {
+    Graph g;
+    std::vector<int64_t> outputs;  // node id, or -1-c for a clear constant c
+    std::string desc;
+    size_t n_inputs = 0;
+};
+
+namespace {
+
+thread_local std::string g_host_err;
+
+struct Builder {
+    fhs_prog &P;
+    StrOps ops;
+    Builder(fhs_prog &p, size_t nbc, size_t nbu) : P(p), ops(p.g, nbc, nbu) {}
+
+    FStr in_str(size_t n_chars) {
+        FStr s;
+        for (size_t i = 0; i < n_chars; i++) {
+            Rad c;
+            for (size_t b = 0; b < ops.nb_char; b++) c.push_back(P.g.input(3));
+            s.ch.push_back(c);
+        }
+        return s;
+    }
+    Rad in_usize() {
+        Rad r;
+        for (size_t b = 0; b < ops.nb_usize; b++) r.push_back(P.g.input(3));
+        return r;
+    }
+    void out_lin(const Lin &e) {
+        if (e.is_const()) { P.outputs.push_back(-1 - (e.c & 31)); return; }
+        P.outputs.push_back(P.g.materialize(e));
+    }
+    void out_rad(const Rad &r) { for (auto &b : r) out_lin(b); }
+    void out_str(const FStr &s) { for (auto &c : s.ch) out_rad(c); }
+};
+
+int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t n_strings,
+             size_t n_usize_args, const uint64_t *scalars, size_t n_scalars) {
+    StrOps &o = B.ops;
+    std::vector<FStr> S;
+    for (size_t i = 0; i < n_strings; i++) {
+        if (n_chars[i] == 0) { g_host_err = "a string has at least its terminator"; return FHS_ERR_INVALID; }
+        S.push_back(B.in_str(n_chars[i]));
+    }
+    std::vector<Rad> U;
+    for (size_t i = 0; i < n_usize_args; i++) U.push_back(B.in_usize());
+    B.P.n_inputs = B.P.g.nodes.size();
+    (void)scalars; (void)n_scalars;
+    auto need = [&](size_t ns, size_t nu) { return n_strings == ns && n_usize_args == nu; };
+    auto bad = [&]() { g_host_err = "wrong operand count for op " + op; return FHS_ERR_INVALID; };
+    auto str_desc = [](const FStr &s) { return "str:" + std::to_string(s.ch.size()); };
+
+    if (op == "is_empty") { if (!need(1, 0)) return bad(); B.out_lin(o.is_empty(S[0])); B.P.desc = "bool"; }
+    else if (op == "len") { if (!need(1, 0)) return bad(); B.out_rad(o.len(S[0])); B.P.desc = "usize"; }
+    else if (op == "eq" || op == "ne" || op == "lt" || op == "le" || op == "gt" || op == "ge" ||
+             op == "eq_ignore_ascii_case" || op == "contains" || op == "starts_with" || op == "ends_with") {
+        if (!need(2, 0)) return bad();
+        Bool r = op == "eq" ? o.eq(S[0], S[1]) : op == "ne" ? o.ne(S[0], S[1]) : op == "lt" ? o.lt(S[0], S[1])
+               : op == "le" ? o.le(S[0], S[1]) : op == "gt" ? o.gt(S[0], S[1]) : op == "ge" ? o.ge(S[0], S[1])
+               : op == "eq_ignore_ascii_case" ? o.eq_ignore_ascii_case(S[0], S[1])
+               : op == "contains" ? o.contains(S[0], S[1]) : op == "starts_with" ? o.starts_with(S[0], S[1])
+               : o.ends_with(S[0], S[1]);
+        B.out_lin(r); B.P.desc = "bool";
+    }
+    else if (op == "find" || op == "rfind") {
+        if (!need(2, 0)) return bad();
+        FOptUsize r = op == "find" ? o.find(S[0], S[1]) : o.rfind(S[0], S[1]);
+        B.out_lin(r.is_some); B.out_rad(r.val); B.P.desc = "opt_usize";
+    }
+    else if (op == "to_uppercase" || op == "to_lowercase" || op == "trim" || op == "trim_start" || op == "trim_end") {
+        if (!need(1, 0)) return bad();
+        FStr r = op == "to_uppercase" ? o.to_uppercase(S[0]) : op == "to_lowercase" ? o.to_lowercase(S[0])
+               : op == "trim" ? o.trim(S[0]) : op == "trim_start" ? o.trim_start(S[0]) : o.trim_end(S[0]);
+        B.out_str(r); B.P.desc = str_desc(r);
+    }
+    else if (op == "strip_prefix" || op == "strip_suffix") {
+        if (!need(2, 0)) return bad();
+        FOptStr r = op == "strip_prefix" ? o.strip_prefix(S[0], S[1]) : o.strip_suffix(S[0], S[1]);
+        B.out_lin(r.is_some); B.out_str(r.val); B.P.desc = "opt_" + str_desc(r.val);
+    }
+    else if (op == "substr_to" || op == "substr_from") {
+        if (!need(1, 1)) return bad();
+        FStr r = op == "substr_to" ? o.substr_to(S[0], U[0]) : o.substr_from(S[0], U[0]);
+        B.out_str(r); B.P.desc = str_desc(r);
+    }
+    else { g_host_err = "unknown op " + op; return FHS_ERR_INVALID; }
+    return FHS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fhs_prog_build(const char *op, const uint32_t *n_chars, size_t n_strings, size_t n_usize_args,
+                   const uint64_t *scalars, size_t n_scalars, uint32_t nbc, uint32_t nbu,
+                   fhs_prog **out) {
+    if (!op || !out || (n_strings && !n_chars) || nbc != 4 || nbu == 0 || nbu > 16) {
+        g_host_err = "fhs_prog_build: bad arguments (num_blocks_char must be 4)";
+        return FHS_ERR_INVALID;
+    }
+    *out = nullptr;
+    fhs_prog *p = new fhs_prog();
+    try {
+        Builder B(*p, nbc, nbu);
+        int rc = build_op(op, B, n_chars, n_strings, n_usize_args, scalars, n_scalars);
+        if (rc != FHS_OK) { delete p; return rc; }
+    } catch (const std::exception &e) {
+        g_host_err = std::string("building ") + op + ": " + e.what();
+        delete p;
+        return FHS_ERR_INVALID;
+    }
+    *out = p;
+    return FHS_OK;
+}
+
+void fhs_prog_destroy(fhs_prog *p) { delete p; }
+
+const char *fhs_host_last_error(void) { return g_host_err.c_str(); }
+
+int fhs_prog_info(const fhs_prog *p, uint64_t info[8]) {
+    if (!p || !info) return FHS_ERR_INVALID;
+    info[0] = p->g.nodes.size();
+    info[1] = p->n_inputs;
+    info[2] = p->outputs.size();
+    info[3] = p->g.terms.size();
+    info[4] = p->g.luts.size();
+    info[5] = (uint64_t)p->g.depth();
+    info[6] = (uint64_t)p->g.pbs_count;
+    info[7] = (uint64_t)(p->g.max_input_noise + 0.999f);
+    return FHS_OK;
+}
+
+const char *fhs_prog_output_desc(const fhs_prog *p) { return p ? p->desc.c_str() : ""; }
+
+int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0, uint32_t *tn,
+                    int64_t *cst, int32_t *level, int32_t *term_src, int32_t *term_coef,
+                    uint64_t *luts, int64_t *outputs) {
+    if (!p) return FHS_ERR_INVALID;
+    const Graph &g = p->g;
+    for (size_t i = 0; i < g.nodes.size(); i++) {
+        const Node &n = g.nodes[i];
+        kind[i] = n.kind; lut[i] = n.lut; t0[i] = n.t0; tn[i] = n.tn; cst[i] = n.c; level[i] = n.level;
+    }
+    for (size_t i = 0; i < g.terms.size(); i++) { term_src[i] = g.terms[i].src; term_coef[i] = g.terms[i].coef; }
+    for (size_t i = 0; i < g.luts.size(); i++) memcpy(luts + 16 * i, g.luts[i].data(), 16 * sizeof(uint64_t));
+    for (size_t i = 0; i < p->outputs.size(); i++) outputs[i] = p->outputs[i];
+    return FHS_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Executor: level by level on a device-resident pool (fhs_pool / fhs_level of include/fhs_cuda.h).
+#include <chrono>
+
+extern "C" int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks,
+                            uint64_t *out_blocks, double stats[4]) {
+    if (!p || !ctx || (!in_blocks && p->n_inputs) || !out_blocks) return FHS_ERR_INVALID;
+    const Graph &g = p->g;
+    fhs_params prm;
+    int rc = fhs_ctx_get_params(ctx, &prm);
+    if (rc != FHS_OK) return rc;
+    const size_t width = (size_t)prm.glwe_dim * prm.poly_size + 1;
+    const uint64_t delta = (1ull << 63) / ((uint64_t)prm.message_modulus * prm.carry_modulus);
+    const size_t N = g.nodes.size();
+    const int D = g.depth();
+    // slots: inputs first, then per level PBS nodes, then the linear outputs of that level
+    std::vector<std::vector<int32_t>> pbs_at(D + 1), lin_at(D + 1);
+    for (size_t i = 0; i < N; i++) {
+        if (g.nodes[i].kind == K_PBS) pbs_at[g.nodes[i].level].push_back((int32_t)i);
+        else if (g.nodes[i].kind == K_LIN) lin_at[g.nodes[i].level].push_back((int32_t)i);
+    }
+    std::vector<uint32_t> slot(N, 0);
+    size_t next = 0;
+    for (size_t i = 0; i < N; i++)
+        if (g.nodes[i].kind == K_INPUT) slot[i] = (uint32_t)next++;
+    if (next != p->n_inputs) return FHS_ERR_INVALID;
+    fhs_pool *pool = nullptr;
+    if ((rc = fhs_pool_create(ctx, N ? N : 1, &pool)) != FHS_OK) return rc;
+    auto t_start = std::chrono::steady_clock::now();
+    const uint64_t launches0 = fhs_launch_count(ctx);
+    uint64_t n_pbs = 0, n_levels = 0;
+    std::vector<uint64_t> tables(g.luts.size() * 16);
+    for (size_t i = 0; i < g.luts.size(); i++) memcpy(&tables[16 * i], g.luts[i].data(), 16 * sizeof(uint64_t));
+    do {
+        if (p->n_inputs && (rc = fhs_pool_write(pool, 0, p->n_inputs, in_blocks)) != FHS_OK) break;
+        std::vector<uint32_t> off, idx, lut;
+        std::vector<int32_t> coef;
+        std::vector<uint64_t> cst;
+        auto run_group = [&](const std::vector<int32_t> &ids, bool is_pbs) -> int {
+            if (ids.empty()) return FHS_OK;
+            off.clear(); idx.clear(); coef.clear(); cst.clear(); lut.clear();
+            off.push_back(0);
+            for (int32_t id : ids) {
+                const Node &n = g.nodes[id];
+                for (uint32_t t = n.t0; t < n.t0 + n.tn; t++) {
+                    idx.push_back(slot[g.terms[t].src]);
+                    coef.push_back(g.terms[t].coef);
+                }
+                off.push_back((uint32_t)idx.size());
+                cst.push_back((uint64_t)n.c * delta);
+                if (is_pbs) lut.push_back((uint32_t)n.lut);
+                slot[id] = (uint32_t)(next + (off.size() - 2));
+            }
+            int r = fhs_level(pool, ids.size(), off.data(), idx.data(), coef.data(), cst.data(),
+                              is_pbs ? lut.data() : nullptr, tables.data(), g.luts.size(), next);
+            next += ids.size();
+            if (is_pbs) { n_pbs += ids.size(); n_levels++; }
+            return r;
+        };
+        for (int l = 0; l <= D && rc == FHS_OK; l++) {
+            if ((rc = run_group(pbs_at[l], true)) != FHS_OK) break;
+            rc = run_group(lin_at[l], false);
+        }
+        if (rc != FHS_OK) break;
+        for (size_t k = 0; k < p->outputs.size() && rc == FHS_OK; k++) {
+            uint64_t *dst = out_blocks + k * width;
+            if (p->outputs[k] < 0) {  // clear constant -> trivial ciphertext
+                memset(dst, 0, width * sizeof(uint64_t));
+                dst[width - 1] = (uint64_t)(-1 - p->outputs[k]) * delta;
+            } else {
+                rc = fhs_pool_read(pool, slot[p->outputs[k]], 1, dst);
+            }
+        }
+    } while (0);
+    fhs_ctx_synchronize(ctx);
+    if (stats) {
+        stats[0] = (double)n_levels;
+        stats[1] = (double)n_pbs;
+        stats[2] = (double)(fhs_launch_count(ctx) - launches0);
+        stats[3] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
+    }
+    fhs_pool_destroy(pool);
+    return rc;
+}

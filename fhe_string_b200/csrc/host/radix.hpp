@@ -226,16 +226,14 @@ struct Ops {
         return r;
     }
     // Sum of radix values of which AT MOST ONE is non-zero (one-hot selections): linear, with an
-    // identity-LUT refresh every 48 addends to bound the noise of the running sum.
+    // identity-LUT refresh whenever the variance of the running sum would exceed 160 PBS outputs.
     Rad onehot_sum(const std::vector<Rad> &v, size_t nblocks) {
         Rad acc = scalar(0, nblocks);
-        size_t pending = 0;
         for (auto &r : v) {
-            for (size_t i = 0; i < nblocks; i++) acc[i] = bounded(add(acc[i], r[i]), 0, 3);
-            if (++pending == 48) {
-                for (size_t i = 0; i < nblocks; i++)
+            for (size_t i = 0; i < nblocks; i++) {
+                if (acc[i].noise + r[i].noise > 160.f)
                     acc[i] = g.pbs(acc[i], [](int x) { return x & 3; }, 0, 3);
-                pending = 1;
+                acc[i] = bounded(add(acc[i], r[i]), 0, 3);
             }
         }
         return acc;

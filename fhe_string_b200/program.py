@@ -1,0 +1,91 @@
+"""ctypes binding of include/fhs_string.h (libfhs_string.so): level programs of fhe_string ops."""
+import ctypes
+import os
+
+import numpy as np
+
+from .engine import FhsError, load_library
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "libfhs_string.so")
+_lib = None
+
+HOST_EXPORTS = ["fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
+                "fhs_prog_output_desc", "fhs_prog_export", "fhs_prog_run"]
+
+
+def load_host_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    load_library()  # libfhs_cuda.so first (dependency)
+    if not os.path.exists(_LIB):
+        raise FhsError(f"{_LIB} is missing: build it with `python -m fhe_string_b200.build`")
+    L = ctypes.CDLL(_LIB)
+    vp, sz = ctypes.c_void_p, ctypes.c_size_t
+    L.fhs_prog_build.argtypes = [ctypes.c_char_p, vp, sz, sz, vp, sz, ctypes.c_uint32, ctypes.c_uint32,
+                                 ctypes.POINTER(vp)]
+    L.fhs_prog_destroy.argtypes = [vp]
+    L.fhs_prog_destroy.restype = None
+    L.fhs_host_last_error.restype = ctypes.c_char_p
+    L.fhs_prog_info.argtypes = [vp, vp]
+    L.fhs_prog_output_desc.argtypes = [vp]
+    L.fhs_prog_output_desc.restype = ctypes.c_char_p
+    L.fhs_prog_export.argtypes = [vp] * 11
+    L.fhs_prog_run.argtypes = [vp, vp, vp, vp, vp]
+    _lib = L
+    return L
+
+
+class Program:
+    """One fhe_string operation compiled for fixed operand shapes."""
+
+    def __init__(self, op, n_chars=(), n_usize_args=0, scalars=(), num_blocks_char=4, num_blocks_usize=4):
+        self.L = load_host_library()
+        self.op = op
+        nc = np.asarray(list(n_chars), dtype=np.uint32)
+        sc = np.asarray(list(scalars), dtype=np.uint64)
+        h = ctypes.c_void_p()
+        rc = self.L.fhs_prog_build(op.encode(), nc.ctypes.data if len(nc) else None, len(nc), int(n_usize_args),
+                                   sc.ctypes.data if len(sc) else None, len(sc), num_blocks_char,
+                                   num_blocks_usize, ctypes.byref(h))
+        if rc != 0:
+            raise FhsError(f"fhs_prog_build({op}) failed ({rc}): {self.L.fhs_host_last_error().decode()}")
+        self.h = h
+        info = np.zeros(8, dtype=np.uint64)
+        self.L.fhs_prog_info(self.h, info.ctypes.data)
+        (self.n_nodes, self.n_inputs, self.n_outputs, self.n_terms, self.n_luts, self.depth, self.pbs_count,
+         self.max_noise) = [int(x) for x in info]
+        self.desc = self.L.fhs_prog_output_desc(self.h).decode()
+        self.nb_char, self.nb_usize = num_blocks_char, num_blocks_usize
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                self.L.fhs_prog_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def export(self):
+        n, t = self.n_nodes, self.n_terms
+        d = dict(kind=np.zeros(n, np.uint8), lut=np.zeros(n, np.int32), t0=np.zeros(n, np.uint32),
+                 tn=np.zeros(n, np.uint32), cst=np.zeros(n, np.int64), level=np.zeros(n, np.int32),
+                 term_src=np.zeros(max(t, 1), np.int32), term_coef=np.zeros(max(t, 1), np.int32),
+                 luts=np.zeros((max(self.n_luts, 1), 16), np.uint64), outputs=np.zeros(self.n_outputs, np.int64))
+        rc = self.L.fhs_prog_export(self.h, *[d[k].ctypes.data for k in
+                                              ("kind", "lut", "t0", "tn", "cst", "level", "term_src", "term_coef",
+                                               "luts", "outputs")])
+        if rc != 0:
+            raise FhsError("fhs_prog_export failed")
+        return d
+
+    def run(self, engine, in_blocks):
+        """in_blocks: u64 [n_inputs][2049] -> (out_blocks [n_outputs][2049], stats dict)."""
+        inb = np.ascontiguousarray(in_blocks, dtype=np.uint64).reshape(self.n_inputs, -1)
+        out = np.empty((self.n_outputs, inb.shape[1] if self.n_inputs else engine.big), dtype=np.uint64)
+        stats = np.zeros(4, dtype=np.float64)
+        rc = self.L.fhs_prog_run(self.h, engine.h, inb.ctypes.data, out.ctypes.data, stats.ctypes.data)
+        if rc != 0:
+            raise FhsError(f"fhs_prog_run({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()}")
+        return out, dict(levels=int(stats[0]), pbs=int(stats[1]), launches=int(stats[2]), ms=float(stats[3]))

@@ -65,6 +65,8 @@ void fhs_ctx_destroy(fhs_ctx *ctx);
  * context's own stream.  Lets a host framework time launches with its own events. */
 int fhs_ctx_set_stream(fhs_ctx *ctx, void *cuda_stream);
 int fhs_ctx_synchronize(fhs_ctx *ctx);
+/* Parameters of the uploaded keys (FHS_ERR_NO_KEYS before fhs_upload_keys). */
+int fhs_ctx_get_params(fhs_ctx *ctx, fhs_params *out);
 
 /* Upload server key material once per GPU (north_star item 3).  Replaces the key held by
  * tfhe::integer::ServerKey (src/lib.rs:64-72).

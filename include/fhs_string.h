@@ -1,0 +1,64 @@
+/*
+ * fhs_string.h -- C ABI of the host-side level scheduler: fhe_string operations compiled to level
+ * programs and executed on the GPU through include/fhs_cuda.h.
+ *
+ * Replaces the bodies of the reference's FheString methods (src/ciphertext/compare.rs:15-151,
+ * convert.rs:14-61, search.rs:17-244, trim.rs:15-132, split.rs:238-515, replace.rs:17-104, mod.rs:132-237):
+ * instead of issuing one tfhe-rs PBS at a time under rayon, an operation is built ONCE per operand
+ * shape as a DAG of LUT evaluations over linear combinations of blocks; all nodes of equal depth
+ * form one level = one fhs_level call.  Ciphertexts are plain tfhe shortint LWE containers
+ * (u64[2049]); operands are passed as arrays of blocks in the reference's own layout:
+ * FheString = chars in order, each FheAsciiChar = 4 blocks little-endian base 4; FheUsize =
+ * num_blocks_usize blocks little-endian; BooleanBlock = 1 block.
+ */
+#ifndef FHS_STRING_H
+#define FHS_STRING_H
+#include <stddef.h>
+#include <stdint.h>
+
+#include "fhs_cuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fhs_prog fhs_prog;
+
+/* Build the program of operation `op` (the reference method name: "eq", "ne", "lt", "le", "gt",
+ * "ge", "eq_ignore_ascii_case", "is_empty", "len", "to_uppercase", "to_lowercase", "contains",
+ * "find", "rfind", "starts_with", "ends_with", "trim", "trim_start", "trim_end", "strip_prefix",
+ * "strip_suffix", "substr_to", "substr_from", ...) for operand shapes:
+ *   n_chars[i] = number of FheAsciiChar of string operand i (terminator and padding included),
+ *   n_usize_args = number of FheUsize operands that follow the strings,
+ *   scalars = clear arguments of the method (e.g. l of replace, clear n), may be NULL.
+ * Returns FHS_ERR_INVALID for unknown ops or shapes the reference would panic on. */
+int fhs_prog_build(const char *op, const uint32_t *n_chars, size_t n_strings, size_t n_usize_args,
+                   const uint64_t *scalars, size_t n_scalars, uint32_t num_blocks_char,
+                   uint32_t num_blocks_usize, fhs_prog **out);
+void fhs_prog_destroy(fhs_prog *p);
+/* Message of the last FHS_ERR_* returned by fhs_prog_build on this thread. */
+const char *fhs_host_last_error(void);
+
+/* Shape of the program. info[0..7] = nodes, input blocks, output blocks, terms, luts, depth (levels),
+ * LUT evaluations (PBS count), max variance multiplier fed to a PBS (rounded up). */
+int fhs_prog_info(const fhs_prog *p, uint64_t info[8]);
+/* Output layout, e.g. "bool", "usize", "str:65", "opt_usize", "opt_str:65", "slices:67:str:65". */
+const char *fhs_prog_output_desc(const fhs_prog *p);
+/* Export for inspection / clear-text evaluation by test code.  Arrays sized from fhs_prog_info:
+ * kind (0 input, 1 pbs, 2 linear), lut, t0, tn, cst (message units), level per node; term_src /
+ * term_coef per term; luts[n_luts][16]; outputs[n_outputs] node ids (-1-c encodes the clear
+ * constant c for outputs that do not depend on any ciphertext). */
+int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0, uint32_t *tn,
+                    int64_t *cst, int32_t *level, int32_t *term_src, int32_t *term_coef,
+                    uint64_t *luts, int64_t *outputs);
+
+/* Execute on the GPU: in_blocks [n_inputs][k*N+1] host -> out_blocks [n_outputs][k*N+1] host.
+ * Ciphertexts stay in a device pool between levels.  stats[0..3] (may be NULL) = levels run,
+ * LUT evaluations, kernels launched, device milliseconds (events around the whole program). */
+int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks, uint64_t *out_blocks,
+                 double stats[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

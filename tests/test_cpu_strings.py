@@ -1,0 +1,104 @@
+"""CPU suite: every string op's level program, evaluated in the clear (oracle/graph_eval.py), against
+Rust std::str semantics (= Python str for ASCII) on the reference's own test tables
+(src/ciphertext/tests/*.rs) and on random inputs."""
+import random
+
+import pytest
+
+from fhe_string_b200.program import Program
+from oracle.graph_eval import eval_clear
+from strutil import WS, decode, enc_chars, to_blocks, usize_blocks
+
+_cache = {}
+
+
+def run(op, strs, pads=None, usizes=(), scalars=(), nbu=4):
+    pads = pads or [None] * len(strs)
+    chars = [enc_chars(s, p) for s, p in zip(strs, pads)]
+    key = (op, tuple(len(c) for c in chars), len(usizes), tuple(scalars), nbu)
+    if key not in _cache:
+        p = Program(op, [len(c) for c in chars], len(usizes), scalars, 4, nbu)
+        _cache[key] = (p, p.export())
+    p, ex = _cache[key]
+    inputs = [b for c in chars for b in to_blocks(c)] + [b for u in usizes for b in usize_blocks(u, nbu)]
+    assert len(inputs) == p.n_inputs
+    assert p.max_noise <= 400, f"{op}: variance multiplier {p.max_noise} fed to a PBS"
+    return decode(p.desc, eval_clear(ex, inputs), nbu)
+
+
+# (input, pattern, pad) rows in the style of tests/search.rs:15-40, tests/compare.rs:67-110
+PAIRS = [("abc", "abc", None, None), ("abc", "abd", None, None), ("abc", "ab", None, None), ("ab", "abc", None, None),
+         ("", "", None, None), ("a", "", None, None), ("", "a", None, None), ("abc", "abc", 5, None),
+         ("abc", "abc", None, 6), ("abc", "abc", 7, 4), ("abc", "b", 5, 3), ("abcabc", "bc", None, None),
+         ("abcabc", "cab", 8, None), ("abc", "abcd", None, None), ("Hello", "hELLO", None, 7),
+         (" A bcbc ", "bc", None, None), ("xxx", "x", None, None), ("zzz", "zzzz", 4, 4)]
+
+
+@pytest.mark.parametrize("a,b,pa,pb", PAIRS)
+def test_compare_ops(a, b, pa, pb):
+    assert run("eq", [a, b], [pa, pb]) == (a == b)
+    assert run("ne", [a, b], [pa, pb]) == (a != b)
+    assert run("lt", [a, b], [pa, pb]) == (a < b)
+    assert run("le", [a, b], [pa, pb]) == (a <= b)
+    assert run("gt", [a, b], [pa, pb]) == (a > b)
+    assert run("ge", [a, b], [pa, pb]) == (a >= b)
+    assert run("eq_ignore_ascii_case", [a, b], [pa, pb]) == (a.lower() == b.lower())
+
+
+@pytest.mark.parametrize("a,b,pa,pb", PAIRS)
+def test_search_ops(a, b, pa, pb):
+    assert run("contains", [a, b], [pa, pb]) == (b in a)
+    f = a.find(b)
+    assert run("find", [a, b], [pa, pb]) == (None if f < 0 else f)
+    r = a.rfind(b)
+    assert run("rfind", [a, b], [pa, pb]) == (None if r < 0 else r)
+    assert run("starts_with", [a, b], [pa, pb]) == a.startswith(b)
+    assert run("ends_with", [a, b], [pa, pb]) == a.endswith(b)
+    assert run("strip_prefix", [a, b], [pa, pb]) == (a[len(b):] if a.startswith(b) else None)
+    assert run("strip_suffix", [a, b], [pa, pb]) == (a[:len(a) - len(b)] if a.endswith(b) else None)
+
+
+@pytest.mark.parametrize("s,pad", [("", None), ("a", None), ("abc", 5), ("  a b  ", None), ("\t\n a\r", 8),
+                                   ("   ", None), ("aZ@[`{z", None), ("Hello, World! 09", 20), (" A bcbc ", None)])
+def test_unary_ops(s, pad):
+    assert run("is_empty", [s], [pad]) == (s == "")
+    assert run("len", [s], [pad]) == len(s)
+    assert run("to_uppercase", [s], [pad]) == s.upper()
+    assert run("to_lowercase", [s], [pad]) == s.lower()
+    assert run("trim", [s], [pad]) == s.strip(WS)
+    assert run("trim_start", [s], [pad]) == s.lstrip(WS)
+    assert run("trim_end", [s], [pad]) == s.rstrip(WS)
+
+
+def test_substr():
+    s = "hello world"
+    for i in (0, 1, 5, 11, 12, 14):
+        assert run("substr_to", [s], [13], usizes=[i]) == s[:i]
+        assert run("substr_from", [s], [13], usizes=[i]) == s[i:]
+
+
+def test_random_against_python_str():
+    rng = random.Random(1234)
+    alphabet = "abAB \t"
+    for _ in range(40):
+        a = "".join(rng.choice(alphabet) for _ in range(rng.randint(0, 7)))
+        b = "".join(rng.choice(alphabet) for _ in range(rng.randint(0, 3)))
+        pa, pb = 8, 4
+        assert run("eq", [a, b], [pa, pb]) == (a == b)
+        assert run("lt", [a, b], [pa, pb]) == (a < b)
+        assert run("contains", [a, b], [pa, pb]) == (b in a)
+        f, r = a.find(b), a.rfind(b)
+        assert run("find", [a, b], [pa, pb]) == (None if f < 0 else f)
+        assert run("rfind", [a, b], [pa, pb]) == (None if r < 0 else r)
+        assert run("ends_with", [a, b], [pa, pb]) == a.endswith(b)
+        assert run("strip_suffix", [a, b], [pa, pb]) == (a[:len(a) - len(b)] if a.endswith(b) else None)
+        assert run("trim", [a], [pa]) == a.strip(WS)
+        assert run("to_uppercase", [a], [pa]) == a.upper()
+        assert run("len", [a], [pa]) == len(a)
+
+
+def test_five_block_usize_long_string():
+    """l >= 256 needs 5-block FheUsize (lib.rs:62; SURVEY.md 7 'parameter trap')."""
+    s = "ab" * 130
+    assert run("len", [s], [260], nbu=5) == 260
+    assert run("find", [s + "c", "bc"], [262, None], nbu=5) == 259

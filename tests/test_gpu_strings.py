@@ -1,0 +1,67 @@
+"""GPU parity: string ops executed as level programs on the B200 (libfhs_string -> libfhs_cuda),
+encrypted with the oracle's client key, decrypted results against std::str semantics
+(the reference's own acceptance criterion, src/ciphertext/tests/*.rs)."""
+import numpy as np
+import pytest
+
+from fhe_string_b200.program import Program
+from strutil import WS, decode, enc_chars, to_blocks, usize_blocks
+
+pytestmark = pytest.mark.gpu
+
+
+def run_gpu(engine, keyset, op, strs, pads=None, usizes=(), nbu=4, seed=0):
+    pads = pads or [None] * len(strs)
+    chars = [enc_chars(s, p) for s, p in zip(strs, pads)]
+    p = Program(op, [len(c) for c in chars], len(usizes), (), 4, nbu)
+    vals = [b for c in chars for b in to_blocks(c)] + [b for u in usizes for b in usize_blocks(u, nbu)]
+    cts = keyset.encrypt(np.array(vals, dtype=np.uint64), seed=seed + 17)
+    out, stats = p.run(engine, cts)
+    dec = [int(x) for x in keyset.decrypt(out)]
+    assert all(0 <= v < 16 for v in dec), dec
+    assert stats["pbs"] == p.pbs_count and stats["levels"] == p.depth
+    return decode(p.desc, dec, nbu), stats
+
+
+def test_cmd_example_config(engine, keyset):
+    """BASELINE configs[0]: examples/cmd --input " A bcbc " --pattern "bc"."""
+    s, pat = " A bcbc ", "bc"
+    assert run_gpu(engine, keyset, "contains", [s, pat])[0] is True
+    assert run_gpu(engine, keyset, "find", [s, pat])[0] == s.find(pat)
+    assert run_gpu(engine, keyset, "rfind", [s, pat])[0] == s.rfind(pat)
+    assert run_gpu(engine, keyset, "starts_with", [s, pat])[0] == s.startswith(pat)
+    assert run_gpu(engine, keyset, "ends_with", [s, pat])[0] == s.endswith(pat)
+    assert run_gpu(engine, keyset, "eq", [s, pat])[0] is False
+    assert run_gpu(engine, keyset, "lt", [s, pat])[0] == (s < pat)
+    assert run_gpu(engine, keyset, "ge", [s, pat])[0] == (s >= pat)
+    assert run_gpu(engine, keyset, "len", [s])[0] == len(s)
+    assert run_gpu(engine, keyset, "is_empty", [s])[0] is False
+    assert run_gpu(engine, keyset, "to_uppercase", [s])[0] == s.upper()
+    assert run_gpu(engine, keyset, "to_lowercase", [s])[0] == s.lower()
+    assert run_gpu(engine, keyset, "trim", [s])[0] == s.strip(WS)
+    assert run_gpu(engine, keyset, "trim_start", [s])[0] == s.lstrip(WS)
+    assert run_gpu(engine, keyset, "trim_end", [s])[0] == s.rstrip(WS)
+    assert run_gpu(engine, keyset, "strip_prefix", [s, " A"])[0] == s[2:]
+    assert run_gpu(engine, keyset, "strip_suffix", [s, "bc "])[0] == s[:-3]
+    assert run_gpu(engine, keyset, "eq_ignore_ascii_case", [s, " a BCBC "])[0] is True
+
+
+def test_padded_64_char_ops(engine, keyset):
+    """BASELINE configs[2]: eq / contains / find on a 64-char padded string, 8-char pattern."""
+    rng = np.random.default_rng(7)
+    s = "".join(chr(int(c)) for c in rng.integers(33, 127, 40))
+    hit, miss = s[13:21], "~~zz~~zz"
+    for pat in (hit, miss):
+        v, st = run_gpu(engine, keyset, "contains", [s, pat], [64, None])
+        assert v == (pat in s)
+        f = s.find(pat)
+        assert run_gpu(engine, keyset, "find", [s, pat], [64, None])[0] == (None if f < 0 else f)
+    assert run_gpu(engine, keyset, "eq", [s, s], [64, 64])[0] is True
+    assert run_gpu(engine, keyset, "eq", [s, s[:-1] + "!"], [64, 64])[0] is False
+    assert run_gpu(engine, keyset, "lt", [s, s[:20] + "~"], [64, 64])[0] == (s < s[:20] + "~")
+
+
+def test_substr_encrypted_index(engine, keyset):
+    s = "hello world"
+    assert run_gpu(engine, keyset, "substr_from", [s], [12], usizes=[6])[0] == s[6:]
+    assert run_gpu(engine, keyset, "substr_to", [s], [12], usizes=[5])[0] == s[:5]
