@@ -5,7 +5,7 @@
 #include <vector>
 
 #include "../../../include/fhs_string.h"
-#include "strings.hpp"
+#include "split.hpp"
 
 using namespace fhs_host;
 
@@ -22,7 +22,7 @@ thread_local std::string g_host_err;
 
 struct Builder {
     fhs_prog &P;
-    StrOps ops;
+    SplitOps ops;
     Builder(fhs_prog &p, size_t nbc, size_t nbu) : P(p), ops(p.g, nbc, nbu) {}
 
     FStr in_str(size_t n_chars) {
@@ -49,7 +49,7 @@ struct Builder {
 
 int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t n_strings,
              size_t n_usize_args, const uint64_t *scalars, size_t n_scalars) {
-    StrOps &o = B.ops;
+    SplitOps &o = B.ops;
     std::vector<FStr> S;
     for (size_t i = 0; i < n_strings; i++) {
         if (n_chars[i] == 0) { g_host_err = "a string has at least its terminator"; return FHS_ERR_INVALID; }
@@ -95,6 +95,29 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
         if (!need(1, 1)) return bad();
         FStr r = op == "substr_to" ? o.substr_to(S[0], U[0]) : o.substr_from(S[0], U[0]);
         B.out_str(r); B.P.desc = str_desc(r);
+    }
+    else if (op == "split" || op == "rsplit" || op == "split_inclusive" || op == "split_terminator" ||
+             op == "rsplit_terminator" || op == "splitn" || op == "rsplitn" || op == "split_ascii_whitespace") {
+        FSliceVec r;
+        if (op == "split_ascii_whitespace") { if (!need(1, 0)) return bad(); r = o.split_ascii_whitespace(S[0]); }
+        else if (op == "splitn" || op == "rsplitn") {
+            if (!need(2, 1)) return bad();
+            r = op == "splitn" ? o.splitn(S[0], U[0], S[1]) : o.rsplitn(S[0], U[0], S[1]);
+        } else {
+            if (!need(2, 0)) return bad();
+            r = op == "split" ? o.split(S[0], S[1]) : op == "rsplit" ? o.rsplit(S[0], S[1])
+              : op == "split_inclusive" ? o.split_inclusive(S[0], S[1])
+              : op == "split_terminator" ? o.split_terminator(S[0], S[1]) : o.rsplit_terminator(S[0], S[1]);
+        }
+        B.out_str(r.s);
+        for (auto &e : r.v) { B.out_lin(e.is_some); B.out_rad(e.start); B.out_rad(e.end); }
+        B.P.desc = "slices:" + std::to_string(r.v.size()) + ":" + str_desc(r.s);
+    }
+    else if (op == "split_once" || op == "rsplit_once") {
+        if (!need(2, 0)) return bad();
+        auto r = o.split_once(S[0], S[1], op == "rsplit_once");
+        B.out_lin(r.is_some); B.out_str(r.first); B.out_str(r.second);
+        B.P.desc = "opt_pair:" + std::to_string(r.first.ch.size()) + ":" + std::to_string(r.second.ch.size());
     }
     else { g_host_err = "unknown op " + op; return FHS_ERR_INVALID; }
     return FHS_OK;

@@ -192,15 +192,18 @@ struct Ops {
     // c ? a : 0   (logic.rs:13 if_then_else_zero -- one PBS per block instead of a radix multiply)
     Rad select_zero(const Bool &c, const Rad &a) {
         Rad r;
-        for (auto &blk : a)
+        for (auto &blk : a) {
+            if (blk.is_const() && blk.c == 0) { r.push_back(Graph::constant(0)); continue; }
             r.push_back(g.pbs(add(scale(c, 4), blk), [](int x) { return x >= 4 ? (x & 3) : 0; }, 0, 3));
+        }
         return r;
     }
     Rad if_then_else(const Bool &c, const Rad &a, const Rad &b) {
         Rad r;
         for (size_t i = 0; i < a.size(); i++) {
-            Lin t = g.pbs(add(scale(c, 4), a[i]), [](int x) { return x >= 4 ? (x & 3) : 0; }, 0, 3);
-            Lin f = g.pbs(add(scale(c, 4), b[i]), [](int x) { return x < 4 ? x : 0; }, 0, 3);
+            const bool az = a[i].is_const() && a[i].c == 0, bz = b[i].is_const() && b[i].c == 0;
+            Lin t = az ? Graph::constant(0) : g.pbs(add(scale(c, 4), a[i]), [](int x) { return x >= 4 ? (x & 3) : 0; }, 0, 3);
+            Lin f = bz ? Graph::constant(0) : g.pbs(add(scale(c, 4), b[i]), [](int x) { return x < 4 ? x : 0; }, 0, 3);
             r.push_back(bounded(add(t, f), 0, 3));
         }
         return r;
@@ -236,6 +239,9 @@ struct Ops {
                 acc[i] = bounded(add(acc[i], r[i]), 0, 3);
             }
         }
+        // callers pack / subtract the result (variance x17 .. x34): hand back fresh digits
+        for (size_t i = 0; i < nblocks; i++)
+            if (acc[i].noise > 10.f) acc[i] = g.pbs(acc[i], [](int x) { return x & 3; }, 0, 3);
         return acc;
     }
 
@@ -285,6 +291,18 @@ struct Ops {
             s.push_back(x);
         }
         return propagate(s);
+    }
+    // cnt + b for a boolean b (ripple over the digits; in a chain over positions the ripples pipeline)
+    Rad inc_if(const Rad &cnt, const Bool &b) {
+        Rad r;
+        Lin carry = b;
+        for (size_t k = 0; k < cnt.size(); k++) {
+            Lin s = bounded(add(cnt[k], carry), 0, 4);
+            if (s.is_const()) { r.push_back(Graph::constant(s.c & 3)); carry = Graph::constant(s.c >> 2); continue; }
+            r.push_back(g.pbs(s, [](int x) { return x & 3; }, 0, 3));
+            if (k + 1 < cnt.size()) carry = (carry.is_const() && carry.c == 0) ? Graph::constant(0) : g.pbs(s, [](int x) { return x >> 2; }, 0, 1);
+        }
+        return r;
     }
     // low bit / high bit of a clean block
     Bool bit0(const Lin &blk) { return g.pbs(blk, [](int x) { return x & 1; }, 0, 1); }

@@ -1,0 +1,131 @@
+// split family (reference src/ciphertext/split.rs:238-515, search.rs:68-152) as level programs.
+// Pieces are described by their END: every non-overlapping match at position c closes a piece
+// [S, c) where S = (previous match) + len(p) (or 0); a final piece [S, len(a)) follows.  This gives
+// Rust's results for every pattern, including the empty one ("abc".split("") = ["","a","b","c",""],
+// tests/split.rs:33-47), without special cases.  The greedy non-overlap decision is the only serial
+// part: one PBS of depth per position.
+#pragma once
+#include <map>
+
+#include "strings.hpp"
+
+namespace fhs_host {
+
+struct SplitOps : StrOps {
+    using StrOps::StrOps;
+
+    // Greedy non-overlapping selection among candidate match starts m[i] for an encrypted pattern
+    // b of at most M chars: chosen[i] = m[i] && no chosen match in the previous len(b)-1 positions
+    // (forward) / next positions (reverse).  gp[d] = [len(b) > d] = [b[d] != 0].
+    std::vector<Bool> non_overlapping(const std::vector<Bool> &m, const std::vector<Bool> &bz, bool reverse) {
+        const size_t L1 = m.size();
+        const size_t M = bz.size() - 1;  // max pattern length
+        std::vector<Bool> chosen(L1);
+        auto at = [&](size_t k) -> size_t { return reverse ? L1 - 1 - k : k; };
+        for (size_t k = 0; k < L1; k++) {
+            // far = sum_{d >= 2} chosen[k-d] & gp[d]   (at most one term is 1)
+            Lin far = Graph::constant(0);
+            for (size_t d = 2; d < M && d <= k; d++)
+                far = add(far, band(chosen[at(k - d)], bnot(bz[d])));
+            far = bounded(far, 0, 1);
+            Lin near = Graph::constant(0);  // chosen[k-1] + gp[1]: busy iff == 2
+            if (k >= 1 && M >= 2) near = add(chosen[at(k - 1)], bnot(bz[1]));
+            Lin x = add(add(scale(m[at(k)], 8), scale(far, 4)), near);
+            chosen[at(k)] = g.pbs(x, [](int v) { return (v >> 3) == 1 && ((v >> 2) & 1) == 0 && (v & 3) < 2; }, 0, 1);
+        }
+        return chosen;
+    }
+
+    enum Mode { SPLIT, INCLUSIVE, TERMINATOR };
+
+    // Common engine.  `limit` (optional) = encrypted maximum number of pieces (splitn).
+    FSliceVec split_engine(const FStr &a, const std::vector<Bool> &chosen, const Rad &plen, Mode mode,
+                           bool reverse_output, const Rad *limit, const std::vector<Bool> *piece_ok) {
+        const size_t L1 = a.ch.size();
+        Rad alen = len(a);
+        std::vector<Bool> keep = chosen;
+        if (limit) {
+            // a match is used only while fewer than limit-1 matches were used before it (scan order)
+            Rad cnt = usize(0);
+            Rad lim1 = sub_rad(*limit, usize(1));          // limit - 1 (limit == 0 handled below)
+            Bool lim_zero = is_zero_rad(*limit);
+            for (size_t k = 0; k < L1; k++) {
+                size_t i = reverse_output ? L1 - 1 - k : k;
+                Bool ok = Ops::lt(cnt, lim1);
+                keep[i] = g.pbs(add(add(chosen[i], ok), bnot(lim_zero)), [](int x) { return x == 3; }, 0, 1);
+                cnt = inc_if(cnt, keep[i]);
+            }
+        }
+        // running piece start S_i (before position i)
+        std::vector<Rad> S(L1 + 1);
+        S[0] = usize(0);
+        for (size_t i = 0; i < L1; i++) {
+            Rad target = add_rad_scalar_len(plen, i);       // i + len(p)
+            S[i + 1] = if_then_else(keep[i], target, S[i]);
+        }
+        FSliceVec out;
+        out.s = a;
+        for (size_t i = 0; i < L1; i++) {
+            FSlice e;
+            e.is_some = keep[i];
+            if (piece_ok) e.is_some = band(keep[i], (*piece_ok)[i]);
+            e.start = S[i];
+            e.end = (mode == INCLUSIVE) ? add_rad_scalar_len(plen, i) : usize(i);
+            out.v.push_back(e);
+        }
+        FSlice fin;
+        fin.start = S[L1];
+        fin.end = alen;
+        if (mode == SPLIT && !piece_ok) fin.is_some = Graph::constant(1);
+        else fin.is_some = Ops::lt(S[L1], alen);                 // drop an empty trailing piece
+        if (limit) fin.is_some = band(fin.is_some, bnot(is_zero_rad(*limit)));
+        out.v.push_back(fin);
+        if (reverse_output) std::reverse(out.v.begin(), out.v.end());
+        return out;
+    }
+    Bool is_zero_rad(const Rad &r) { return is_zero(r); }
+    // memoised i + len(p)
+    std::map<size_t, Rad> plen_cache;
+    const Rad *plen_key = nullptr;
+    Rad add_rad_scalar_len(const Rad &plen, size_t i) {
+        if (plen_key != &plen) { plen_cache.clear(); plen_key = &plen; }
+        auto it = plen_cache.find(i);
+        if (it != plen_cache.end()) return it->second;
+        Rad r = i == 0 ? plen : add_scalar(plen, i);
+        plen_cache[i] = r;
+        return r;
+    }
+
+    FSliceVec split_pattern(const FStr &a, const FStr &b, Mode mode, bool reverse, const Rad *limit) {
+        std::vector<Bool> az = zero_mask(a), bz = zero_mask(b);
+        std::vector<Bool> m = find_all(a, b, az, true);
+        std::vector<Bool> chosen = non_overlapping(m, bz, reverse);
+        Rad plen = len_from_mask(bz);
+        return split_engine(a, chosen, plen, mode, reverse, limit, nullptr);
+    }
+    // split.rs:339-413
+    FSliceVec split(const FStr &a, const FStr &b) { return split_pattern(a, b, SPLIT, false, nullptr); }
+    FSliceVec rsplit(const FStr &a, const FStr &b) { return split_pattern(a, b, SPLIT, true, nullptr); }
+    FSliceVec split_inclusive(const FStr &a, const FStr &b) { return split_pattern(a, b, INCLUSIVE, false, nullptr); }
+    FSliceVec split_terminator(const FStr &a, const FStr &b) { return split_pattern(a, b, TERMINATOR, false, nullptr); }
+    FSliceVec rsplit_terminator(const FStr &a, const FStr &b) { return split_pattern(a, b, TERMINATOR, true, nullptr); }
+    FSliceVec splitn(const FStr &a, const Rad &n, const FStr &b) { return split_pattern(a, b, SPLIT, false, &n); }
+    FSliceVec rsplitn(const FStr &a, const Rad &n, const FStr &b) { return split_pattern(a, b, SPLIT, true, &n); }
+    // split.rs:415  separators are single whitespace chars, empty pieces are dropped
+    FSliceVec split_ascii_whitespace(const FStr &a) {
+        std::vector<Bool> ws, ok;
+        for (auto &c : a.ch) ws.push_back(is_whitespace(c));
+        for (size_t i = 0; i < a.ch.size(); i++) ok.push_back(i == 0 ? Graph::constant(0) : bnot(ws[i - 1]));
+        Rad one = usize(1);
+        return split_engine(a, ws, one, SPLIT, false, nullptr, &ok);
+    }
+    // split.rs:505/511
+    struct OnceResult { Bool is_some; FStr first, second; };
+    OnceResult split_once(const FStr &a, const FStr &b, bool reverse) {
+        FOptUsize f = reverse ? rfind(a, b) : find(a, b);
+        Rad after = add_rad(f.val, len(b));
+        return OnceResult{f.is_some, substr_to(a, f.val), shift_left(a, after)};
+    }
+};
+
+}  // namespace fhs_host

@@ -40,6 +40,10 @@ def decode(desc, out, nbu=4):
         return from_blocks(out[1:], nbu)[0] if out[0] else None
     if desc.startswith("opt_str:"):
         return dec_str(out[1:]) if out[0] else None
+    if desc.startswith("opt_pair:"):
+        _, n1, n2 = desc.split(":")
+        n1 = int(n1)
+        return (dec_str(out[1:1 + 4 * n1]), dec_str(out[1 + 4 * n1:])) if out[0] else None
     if desc.startswith("slices:"):
         # slices:<n_entries>:str:<n_chars>  -> [string blocks][(is_some, start, end)]*
         _, n_entries, _, n_chars = desc.split(":")

@@ -102,3 +102,58 @@ def test_five_block_usize_long_string():
     s = "ab" * 130
     assert run("len", [s], [260], nbu=5) == 260
     assert run("find", [s + "c", "bc"], [262, None], nbu=5) == 259
+
+
+def rust_split_inclusive(s, p):
+    out, i = [], 0
+    if p == "":   # Rust: "abc".split_inclusive("") == ["a", "b", "c"] -- matches at 0 close empty piece... see below
+        return None
+    while True:
+        j = s.find(p, i)
+        if j < 0:
+            break
+        out.append(s[i:j + len(p)])
+        i = j + len(p)
+    if i < len(s):
+        out.append(s[i:])
+    return out
+
+
+SPLIT_ROWS = [("a,b,c", ",", None, None), ("xxx", "x", None, None), ("xxx", "xx", None, None), ("abc", "", None, None),
+              ("", "x", None, None), ("", "", None, None), ("a,b,", ",", 6, 2), (",a", ",", None, 3),
+              ("abcabca", "abc", 9, None), (" A bcbc ", "bc", None, None), ("aaaa", "aa", 5, 3)]
+
+
+@pytest.mark.parametrize("s,p,ps,pp", SPLIT_ROWS)
+def test_split_family(s, p, ps, pp):
+    if p != "":
+        assert run("split", [s, p], [ps, pp]) == s.split(p)
+        assert run("rsplit", [s, p], [ps, pp]) == s.rsplit(p)[::-1]
+        term = s.split(p)
+        if term and term[-1] == "":
+            term = term[:-1]
+        assert run("split_terminator", [s, p], [ps, pp]) == term
+        term_r = s.rsplit(p)           # right-to-left non-overlapping search (search.rs:114-152)
+        if term_r and term_r[-1] == "":
+            term_r = term_r[:-1]
+        assert run("rsplit_terminator", [s, p], [ps, pp]) == term_r[::-1]
+        assert run("split_inclusive", [s, p], [ps, pp]) == rust_split_inclusive(s, p)
+        for n in (0, 1, 2, 3, 9):
+            want = [] if n == 0 else s.split(p, n - 1)
+            assert run("splitn", [s, p], [ps, pp], usizes=[n]) == want
+            want = [] if n == 0 else s.rsplit(p, n - 1)[::-1]
+            assert run("rsplitn", [s, p], [ps, pp], usizes=[n]) == want
+        f = s.find(p)
+        assert run("split_once", [s, p], [ps, pp]) == (None if f < 0 else (s[:f], s[f + len(p):]))
+        r = s.rfind(p)
+        assert run("rsplit_once", [s, p], [ps, pp]) == (None if r < 0 else (s[:r], s[r + len(p):]))
+    else:
+        # Rust: "abc".split("") == ["", "a", "b", "c", ""] (tests/split.rs:33-47)
+        assert run("split", [s, p], [ps, pp]) == [""] + list(s) + [""]
+        assert run("rsplit", [s, p], [ps, pp]) == ([""] + list(s) + [""])[::-1]
+
+
+@pytest.mark.parametrize("s,pad", [("a b  c", None), ("  lead and trail \t", 20), ("", None), ("   ", 4), ("one", 5),
+                                   ("a\tb\nc\rd", None)])
+def test_split_ascii_whitespace(s, pad):
+    assert run("split_ascii_whitespace", [s], [pad]) == s.split()
