@@ -5,7 +5,7 @@
 #include <vector>
 
 #include "../../../include/fhs_string.h"
-#include "split.hpp"
+#include "replace.hpp"
 
 using namespace fhs_host;
 
@@ -22,7 +22,7 @@ thread_local std::string g_host_err;
 
 struct Builder {
     fhs_prog &P;
-    SplitOps ops;
+    ReplaceOps ops;
     Builder(fhs_prog &p, size_t nbc, size_t nbu) : P(p), ops(p.g, nbc, nbu) {}
 
     FStr in_str(size_t n_chars) {
@@ -49,7 +49,7 @@ struct Builder {
 
 int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t n_strings,
              size_t n_usize_args, const uint64_t *scalars, size_t n_scalars) {
-    SplitOps &o = B.ops;
+    ReplaceOps &o = B.ops;
     std::vector<FStr> S;
     for (size_t i = 0; i < n_strings; i++) {
         if (n_chars[i] == 0) { g_host_err = "a string has at least its terminator"; return FHS_ERR_INVALID; }
@@ -58,7 +58,6 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
     std::vector<Rad> U;
     for (size_t i = 0; i < n_usize_args; i++) U.push_back(B.in_usize());
     B.P.n_inputs = B.P.g.nodes.size();
-    (void)scalars; (void)n_scalars;
     auto need = [&](size_t ns, size_t nu) { return n_strings == ns && n_usize_args == nu; };
     auto bad = [&]() { g_host_err = "wrong operand count for op " + op; return FHS_ERR_INVALID; };
     auto str_desc = [](const FStr &s) { return "str:" + std::to_string(s.ch.size()); };
@@ -118,6 +117,15 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
         auto r = o.split_once(S[0], S[1], op == "rsplit_once");
         B.out_lin(r.is_some); B.out_str(r.first); B.out_str(r.second);
         B.P.desc = "opt_pair:" + std::to_string(r.first.ch.size()) + ":" + std::to_string(r.second.ch.size());
+    }
+    else if (op == "replace" || op == "replacen") {
+        // operands: a, p, s [, n]; scalars[0] = l, the output capacity (replace.rs:17,23), clamped
+        // to the maximum string length like replace.rs:45
+        if (!(n_strings == 3 && n_usize_args == (op == "replacen" ? 1u : 0u)) || n_scalars < 1) return bad();
+        uint64_t maxlen = (o.nb_usize >= 16) ? ~0ull : ((1ull << (2 * o.nb_usize)) - 1);
+        size_t l = (size_t)std::min<uint64_t>(scalars[0], maxlen);
+        FStr r = op == "replace" ? o.replace(S[0], S[1], S[2], l) : o.replacen(S[0], S[1], S[2], U[0], l);
+        B.out_str(r); B.P.desc = str_desc(r);
     }
     else { g_host_err = "unknown op " + op; return FHS_ERR_INVALID; }
     return FHS_OK;

@@ -1,0 +1,111 @@
+// replace / replacen (reference src/ciphertext/replace.rs:17-104) as a level program.
+// The reference walks the OUTPUT serially with char_at / element_at per position.  Here the result
+// is a concatenation of per-position segments  seg_i = (match starts at i ? s : "") ++ (i covered by
+// a match ? "" : a[i])  built by a balanced tree of encrypted-length concatenations:
+//   concat(A, B) = A + shift_right(B, len(A))   (blockwise add: the operands never overlap)
+// so the depth is O(log^2 L) instead of O(L) and all shifts of one tree level share their levels.
+#pragma once
+#include "split.hpp"
+
+namespace fhs_host {
+
+struct ReplaceOps : SplitOps {
+    using SplitOps::SplitOps;
+
+    struct Buf { std::vector<Rad> ch; Rad len; size_t max_len; };  // chars beyond len are 0
+
+    static bool rad_is_zero_const(const Rad &r) {
+        for (auto &b : r) if (!(b.is_const() && b.c == 0)) return false;
+        return true;
+    }
+    Rad add_chars(const Rad &x, const Rad &y) {  // disjoint supports: at most one is non-zero
+        Rad r;
+        for (size_t k = 0; k < x.size(); k++) r.push_back(bounded(add(x[k], y[k]), 0, 3));
+        return r;
+    }
+    // B shifted right by `amount` (<= max_amount) inside a buffer of `cap` chars
+    std::vector<Rad> shift_right(const std::vector<Rad> &b, const Rad &amount, size_t max_amount, size_t cap) {
+        Rad z = zero_char();
+        std::vector<Rad> cur(cap, z);
+        for (size_t j = 0; j < std::min(cap, b.size()); j++) cur[j] = b[j];
+        for (size_t blk = 0; blk < amount.size(); blk++) {
+            for (int bit = 0; bit < 2; bit++) {
+                const size_t sh = (size_t)1 << (2 * blk + bit);
+                if (sh > max_amount) return cur;
+                Bool sb = bit ? bit1(amount[blk]) : bit0(amount[blk]);
+                if (sb.is_const() && sb.c == 0) continue;
+                std::vector<Rad> nx(cap);
+                for (size_t j = 0; j < cap; j++) {
+                    const Rad &from = (j >= sh) ? cur[j - sh] : z;
+                    if (rad_is_zero_const(from) && rad_is_zero_const(cur[j])) { nx[j] = z; continue; }
+                    nx[j] = if_then_else(sb, from, cur[j]);
+                }
+                cur.swap(nx);
+            }
+        }
+        return cur;
+    }
+    Buf concat(const Buf &A, const Buf &B, size_t limit) {
+        Buf R;
+        R.max_len = std::min(A.max_len + B.max_len, limit);
+        const size_t cap = R.max_len;
+        std::vector<Rad> bs = shift_right(B.ch, A.len, A.max_len, cap);
+        Rad z = zero_char();
+        for (size_t j = 0; j < cap; j++) R.ch.push_back(j < A.ch.size() ? add_chars(A.ch[j], bs[j]) : bs[j]);
+        R.len = add_rad(A.len, B.len);
+        return R;
+    }
+
+    // replace.rs:37 replace_opt; n == nullptr replaces every match
+    FStr replace_impl(const FStr &a, const FStr &p, const FStr &s, const Rad *n, size_t l) {
+        const size_t L1 = a.ch.size(), Ms = s.ch.size() - 1, Mp = p.ch.size() - 1;
+        std::vector<Bool> az = zero_mask(a), pz = zero_mask(p), sz = zero_mask(s);
+        std::vector<Bool> m = find_all(a, p, az, true);
+        std::vector<Bool> chosen = non_overlapping(m, pz, false);
+        if (n) {
+            Rad cnt = usize(0);
+            for (size_t i = 0; i < L1; i++) {
+                Bool ok = Ops::lt(cnt, *n);
+                chosen[i] = band(chosen[i], ok);
+                cnt = inc_if(cnt, chosen[i]);
+            }
+        }
+        Rad slen = len_from_mask(sz);
+        std::vector<Buf> nodes;
+        for (size_t i = 0; i < L1; i++) {
+            // covered_i = sum_{d < Mp} chosen[i-d] & [len(p) > d]   (at most one term)
+            Lin cov = Graph::constant(0);
+            for (size_t d = 0; d < Mp && d <= i; d++) cov = add(cov, band(chosen[i - d], bnot(pz[d])));
+            cov = bounded(cov, 0, 1);
+            if (Ms > 0) {
+                Buf seg;
+                seg.max_len = Ms;
+                for (size_t t = 0; t < Ms; t++) seg.ch.push_back(select_zero(chosen[i], s.ch[t]));
+                seg.len = select_zero(chosen[i], slen);
+                nodes.push_back(seg);
+            }
+            Buf lit;
+            lit.max_len = 1;
+            Bool keep = bnot(cov);
+            lit.ch.push_back(select_zero(keep, a.ch[i]));
+            Bool nonzero = g.pbs(add(keep, bnot(az[i])), [](int x) { return x == 2; }, 0, 1);
+            lit.len = from_bool(nonzero, nb_usize);
+            nodes.push_back(lit);
+        }
+        while (nodes.size() > 1) {
+            std::vector<Buf> nx;
+            for (size_t i = 0; i + 1 < nodes.size(); i += 2) nx.push_back(concat(nodes[i], nodes[i + 1], l));
+            if (nodes.size() & 1) nx.push_back(nodes.back());
+            nodes.swap(nx);
+        }
+        FStr out;
+        Rad z = zero_char();
+        for (size_t j = 0; j < l; j++) out.ch.push_back(j < nodes[0].ch.size() ? nodes[0].ch[j] : z);
+        out.ch.push_back(z);  // terminator
+        return out;
+    }
+    FStr replace(const FStr &a, const FStr &p, const FStr &s, size_t l) { return replace_impl(a, p, s, nullptr, l); }
+    FStr replacen(const FStr &a, const FStr &p, const FStr &s, const Rad &n, size_t l) { return replace_impl(a, p, s, &n, l); }
+};
+
+}  // namespace fhs_host

@@ -157,3 +157,19 @@ def test_split_family(s, p, ps, pp):
                                    ("a\tb\nc\rd", None)])
 def test_split_ascii_whitespace(s, pad):
     assert run("split_ascii_whitespace", [s], [pad]) == s.split()
+
+
+REPLACE_ROWS = [("abcabc", "bc", "X", None, None, None), ("abcabc", "bc", "", None, None, None),
+                ("abcabc", "b", "xyz", 8, 2, 4), ("aaa", "aa", "b", None, None, None), ("abc", "", "-", None, None, None),
+                ("", "", "x", None, None, None), ("abc", "abc", "", 5, 4, 2), ("abc", "d", "x", None, None, None),
+                (" A bcbc ", "bc", "_", None, None, None), ("xxxx", "x", "yy", None, None, None)]
+
+
+@pytest.mark.parametrize("a,p,s,pa,pp,ps", REPLACE_ROWS)
+def test_replace(a, p, s, pa, pp, ps):
+    want = a.replace(p, s)
+    assert run("replace", [a, p, s], [pa, pp, ps], scalars=[len(want)]) == want
+    assert run("replace", [a, p, s], [pa, pp, ps], scalars=[len(want) + 3]) == want
+    for n in (0, 1, 2, 5):
+        wn = a.replace(p, s, n)
+        assert run("replacen", [a, p, s], [pa, pp, ps], usizes=[n], scalars=[len(wn) + 1]) == wn

@@ -65,3 +65,24 @@ def test_substr_encrypted_index(engine, keyset):
     s = "hello world"
     assert run_gpu(engine, keyset, "substr_from", [s], [12], usizes=[6])[0] == s[6:]
     assert run_gpu(engine, keyset, "substr_to", [s], [12], usizes=[5])[0] == s[:5]
+
+
+def test_split_and_replace_cmd_config(engine, keyset):
+    """split / replace rows of examples/cmd on " A bcbc " with pattern "bc", substitution "_"."""
+    s, pat, sub = " A bcbc ", "bc", "_"
+    assert run_gpu(engine, keyset, "split", [s, pat])[0] == s.split(pat)
+    assert run_gpu(engine, keyset, "rsplit", [s, pat])[0] == s.rsplit(pat)[::-1]
+    assert run_gpu(engine, keyset, "split_inclusive", [s, pat])[0] == [" A bc", "bc", " "]
+    assert run_gpu(engine, keyset, "split_terminator", [s, pat])[0] == s.split(pat)
+    assert run_gpu(engine, keyset, "split_ascii_whitespace", [s])[0] == s.split()
+    assert run_gpu(engine, keyset, "splitn", [s, pat], usizes=[2])[0] == s.split(pat, 1)
+    assert run_gpu(engine, keyset, "rsplitn", [s, pat], usizes=[2])[0] == s.rsplit(pat, 1)[::-1]
+    assert run_gpu(engine, keyset, "split_once", [s, pat])[0] == tuple(s.split(pat, 1))
+    assert run_gpu(engine, keyset, "rsplit_once", [s, pat])[0] == tuple(s.rsplit(pat, 1))
+    want = s.replace(pat, sub)
+    p_chars = [enc_chars(x) for x in (s, pat, sub)]
+    for op, usz, w in (("replace", (), want), ("replacen", (1,), s.replace(pat, sub, 1))):
+        p = Program(op, [len(c) for c in p_chars], len(usz), (len(w),), 4, 4)
+        vals = [b for c in p_chars for b in to_blocks(c)] + [b for u in usz for b in usize_blocks(u)]
+        out, _ = p.run(engine, keyset.encrypt(np.array(vals, dtype=np.uint64), seed=5))
+        assert decode(p.desc, [int(x) for x in keyset.decrypt(out)]) == w
