@@ -1,0 +1,267 @@
+"""Python mirror of the reference's public API (src/lib.rs, src/client_key.rs, src/server_key.rs,
+src/ciphertext/*.rs): generate_keys, ClientKey, ServerKey, FheString / FheUsize / FheOption /
+FheStringSliceVector with the same method names and argument meaning.  Server methods compile the
+operation to a level program (libfhs_string) and run it on the GPU (libfhs_cuda)."""
+import ctypes
+
+import numpy as np
+
+from .engine import Engine, FhsError, Params
+from .program import Program, load_host_library
+
+
+def _client_lib():
+    L = load_host_library()
+    if not getattr(L, "_client_bound", False):
+        vp, sz = ctypes.c_void_p, ctypes.c_size_t
+        L.fhs_generate_keys.argtypes = [vp, vp, sz, ctypes.c_uint64, ctypes.POINTER(vp)]
+        L.fhs_client_key_destroy.argtypes = [vp]
+        L.fhs_client_key_destroy.restype = None
+        L.fhs_client_last_error.restype = ctypes.c_char_p
+        L.fhs_client_key_info.argtypes = [vp, vp, vp, vp, vp]
+        L.fhs_client_ksk.argtypes = [vp, vp]
+        L.fhs_client_ksk.restype = ctypes.POINTER(ctypes.c_uint64)
+        L.fhs_client_bsk.argtypes = [vp, vp]
+        L.fhs_client_bsk.restype = ctypes.POINTER(ctypes.c_uint64)
+        L.fhs_encrypt_blocks.argtypes = [vp, vp, sz, vp]
+        L.fhs_decrypt_blocks.argtypes = [vp, vp, sz, vp]
+        L.fhs_string_layout.argtypes = [vp, ctypes.c_char_p, ctypes.c_int64, vp, sz, vp]
+        L._client_bound = True
+    return L
+
+
+class ClientKey:
+    """src/client_key.rs:16-62."""
+
+    def __init__(self, l=255, seed=0, params=None):
+        self.L = _client_lib()
+        h = ctypes.c_void_p()
+        rc = self.L.fhs_generate_keys(ctypes.byref(params) if params is not None else None, None, int(l),
+                                      int(seed), ctypes.byref(h))
+        if rc != 0:
+            raise FhsError(self.L.fhs_client_last_error().decode())
+        self.h = h
+        self.p = Params()
+        nbc, nbu, ml = ctypes.c_uint32(), ctypes.c_uint32(), ctypes.c_size_t()
+        self.L.fhs_client_key_info(self.h, ctypes.byref(self.p), ctypes.byref(nbc), ctypes.byref(nbu), ctypes.byref(ml))
+        self.num_blocks_char, self.num_blocks_usize, self.max_len = nbc.value, nbu.value, ml.value
+        self.big = self.p.glwe_dim * self.p.poly_size + 1
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                self.L.fhs_client_key_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def msg_mod(self):
+        return self.p.message_modulus
+
+    def ksk(self):
+        n = ctypes.c_size_t()
+        ptr = self.L.fhs_client_ksk(self.h, ctypes.byref(n))
+        return np.ctypeslib.as_array(ptr, shape=(n.value,))
+
+    def bsk(self):
+        n = ctypes.c_size_t()
+        ptr = self.L.fhs_client_bsk(self.h, ctypes.byref(n))
+        return np.ctypeslib.as_array(ptr, shape=(n.value,))
+
+    def encrypt_blocks(self, msgs):
+        msgs = np.ascontiguousarray(msgs, dtype=np.uint64).reshape(-1)
+        out = np.empty((len(msgs), self.big), dtype=np.uint64)
+        if self.L.fhs_encrypt_blocks(self.h, msgs.ctypes.data, len(msgs), out.ctypes.data) != 0:
+            raise FhsError("encrypt failed")
+        return out
+
+    def decrypt_blocks(self, cts):
+        cts = np.ascontiguousarray(cts, dtype=np.uint64).reshape(-1, self.big)
+        out = np.empty(len(cts), dtype=np.uint64)
+        if self.L.fhs_decrypt_blocks(self.h, cts.ctypes.data, len(cts), out.ctypes.data) != 0:
+            raise FhsError("decrypt failed")
+        return out
+
+    def _radix(self, blocks, nb):
+        v = self.decrypt_blocks(blocks)
+        return [int(sum(int(v[i + k]) << (2 * k) for k in range(nb))) for i in range(0, len(v), nb)]
+
+    # client_key.rs:23-43
+    def encrypt_usize(self, v):
+        nb = self.num_blocks_usize
+        return FheUsize(self.encrypt_blocks([(int(v) >> (2 * k)) & 3 for k in range(nb)]))
+
+    def decrypt_usize(self, ct):
+        return self._radix(ct.blocks, self.num_blocks_usize)[0] % (4 ** self.num_blocks_usize)
+
+    def decrypt_bool(self, ct):
+        return int(self.decrypt_blocks(ct.blocks)[0]) != 0
+
+    def encrypt_str(self, s, l=None):
+        """FheString::new (mod.rs:58-92); raises ValueError with the reference's messages."""
+        if any(ord(c) >= 128 for c in s):
+            raise ValueError("string is not ascii")
+        if "\0" in s:
+            raise ValueError("string contains terminator character")
+        n = ctypes.c_size_t()
+        pad = -1 if l is None else int(l)
+        rc = self.L.fhs_string_layout(self.h, s.encode("ascii"), pad, None, 0, ctypes.byref(n))
+        if rc != 0:
+            raise ValueError(self.L.fhs_client_last_error().decode())
+        vals = np.zeros(n.value * self.num_blocks_char, dtype=np.uint64)
+        self.L.fhs_string_layout(self.h, s.encode("ascii"), pad, vals.ctypes.data, len(vals), ctypes.byref(n))
+        return FheString(self.encrypt_blocks(vals))
+
+    def decrypt_str(self, fs):
+        chars = self._radix(fs.blocks, self.num_blocks_char)
+        return "".join(chr(c % 256) for c in chars if c % 256 != 0)
+
+
+class ServerKey:
+    """src/server_key.rs:12-33: key material on the GPU + program cache."""
+
+    def __init__(self, ck, device=0):
+        self.engine = Engine(device)
+        self.engine.upload_keys(ck.p, ck.ksk(), ck.bsk(), ksk_level_order=0)
+        self.num_blocks_char, self.num_blocks_usize = ck.num_blocks_char, ck.num_blocks_usize
+        self.max_len = ck.max_len
+        self._progs = {}
+        self.last_stats = None
+
+    def msg_mod(self):
+        return self.engine.p.message_modulus
+
+    def run(self, op, strings=(), usizes=(), scalars=()):
+        key = (op, tuple(s.n_chars for s in strings), len(usizes), tuple(scalars))
+        p = self._progs.get(key)
+        if p is None:
+            p = Program(op, [s.n_chars for s in strings], len(usizes), scalars, self.num_blocks_char,
+                        self.num_blocks_usize)
+            self._progs[key] = p
+        parts = [s.blocks for s in strings] + [u.blocks for u in usizes]
+        inb = np.concatenate(parts) if parts else np.zeros((0, self.engine.big), np.uint64)
+        out, self.last_stats = p.run(self.engine, inb)
+        return _wrap(p.desc, out, self.num_blocks_usize)
+
+
+def generate_keys(l=255, seed=0, device=0):
+    """src/lib.rs:44-77: (ClientKey, ServerKey) for PARAM_MESSAGE_2_CARRY_2_KS_PBS, max length l."""
+    ck = ClientKey(l=l, seed=seed)
+    return ck, ServerKey(ck, device)
+
+
+class BooleanBlock:
+    def __init__(self, blocks):
+        self.blocks = blocks
+
+    def decrypt(self, k):
+        return k.decrypt_bool(self)
+
+
+class FheUsize:
+    def __init__(self, blocks):
+        self.blocks = blocks
+
+    def decrypt(self, k):
+        return k.decrypt_usize(self)
+
+
+class FheOption:
+    """mod.rs:358-399: is_some + val; decrypt gives None when is_some is false."""
+
+    def __init__(self, is_some, val):
+        self.is_some, self.val = is_some, val
+
+    def decrypt(self, k):
+        if not self.is_some.decrypt(k):
+            return None
+        if isinstance(self.val, tuple):
+            return tuple(v.decrypt(k) for v in self.val)
+        return self.val.decrypt(k)
+
+
+class FheStringSliceVector:
+    """split.rs:21-231: the string + candidate (is_some, start, end) entries."""
+
+    def __init__(self, s, entries):
+        self.s, self.v = s, entries
+
+    def decrypt(self, k):
+        s = self.s.decrypt(k)
+        out = []
+        for is_some, start, end in self.v:
+            if is_some.decrypt(k):
+                a, b = start.decrypt(k), end.decrypt(k)
+                out.append(s[a:b] if a <= b else "")
+        return out
+
+
+def _wrap(desc, out, nbu):
+    if desc == "bool":
+        return BooleanBlock(out[:1])
+    if desc == "usize":
+        return FheUsize(out[:nbu])
+    if desc.startswith("str:"):
+        return FheString(out)
+    if desc == "opt_usize":
+        return FheOption(BooleanBlock(out[:1]), FheUsize(out[1:1 + nbu]))
+    if desc.startswith("opt_str:"):
+        return FheOption(BooleanBlock(out[:1]), FheString(out[1:]))
+    if desc.startswith("opt_pair:"):
+        _, n1, _n2 = desc.split(":")
+        n1 = int(n1) * 4
+        return FheOption(BooleanBlock(out[:1]), (FheString(out[1:1 + n1]), FheString(out[1 + n1:])))
+    if desc.startswith("slices:"):
+        _, n_entries, _, n_chars = desc.split(":")
+        p = 4 * int(n_chars)
+        s = FheString(out[:p])
+        ents = []
+        for _ in range(int(n_entries)):
+            ents.append((BooleanBlock(out[p:p + 1]), FheUsize(out[p + 1:p + 1 + nbu]),
+                         FheUsize(out[p + 1 + nbu:p + 1 + 2 * nbu])))
+            p += 1 + 2 * nbu
+        return FheStringSliceVector(s, ents)
+    raise ValueError(desc)
+
+
+class FheString:
+    """mod.rs:43-47: Vec<FheAsciiChar>, 0-terminated; blocks = [n_chars * 4][2049] u64."""
+
+    def __init__(self, blocks):
+        self.blocks = np.ascontiguousarray(blocks, dtype=np.uint64)
+        self.n_chars = len(self.blocks) // 4
+
+    def decrypt(self, k):
+        return k.decrypt_str(self)
+
+    def max_len(self):
+        return self.n_chars - 1
+
+
+def _unary(name):
+    def f(self, k):
+        return k.run(name, [self])
+    f.__name__ = name
+    return f
+
+
+def _binary(name):
+    def f(self, k, s):
+        return k.run(name, [self, s])
+    f.__name__ = name
+    return f
+
+
+for _n in ("is_empty", "len", "to_uppercase", "to_lowercase", "trim", "trim_start", "trim_end",
+           "split_ascii_whitespace"):
+    setattr(FheString, _n, _unary(_n))
+for _n in ("eq", "ne", "lt", "le", "gt", "ge", "eq_ignore_ascii_case", "contains", "find", "rfind",
+           "starts_with", "ends_with", "strip_prefix", "strip_suffix", "split", "rsplit", "split_inclusive",
+           "split_terminator", "rsplit_terminator", "split_once", "rsplit_once"):
+    setattr(FheString, _n, _binary(_n))
+FheString.substr_to = lambda self, k, index: k.run("substr_to", [self], [index])
+FheString.substr_from = lambda self, k, index: k.run("substr_from", [self], [index])
+FheString.splitn = lambda self, k, n, p: k.run("splitn", [self, p], [n])
+FheString.rsplitn = lambda self, k, n, p: k.run("rsplitn", [self, p], [n])
+FheString.replace = lambda self, k, p, s, l: k.run("replace", [self, p, s], (), (int(l),))
+FheString.replacen = lambda self, k, p, s, n, l: k.run("replacen", [self, p, s], [n], (int(l),))

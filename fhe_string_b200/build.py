@@ -59,7 +59,7 @@ def build_host(force=False):
         os.path.join(HERE, "..", "include", "fhs_string.h"), os.path.join(HERE, "..", "include", "fhs_cuda.h"), LIB]
     if force or _stale(HOST_LIB, deps):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-o", HOST_LIB] + srcs +
-                              ["-L" + HERE, "-lfhs_cuda", "-Wl,-rpath,$ORIGIN"])
+                              ["-L" + HERE, "-lfhs_cuda", "-Wl,-rpath,$ORIGIN", "-lpthread"])
     return HOST_LIB
 
 

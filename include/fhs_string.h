@@ -58,6 +58,26 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
 int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks, uint64_t *out_blocks,
                  double stats[4]);
 
+/* ---- client side (CPU): generate_keys / ClientKey of the reference ---------------------------
+ * src/lib.rs:44-77 generate_keys_with_params(p, l); src/client_key.rs:16-62; mod.rs:58-92,121-129.
+ * Not accelerated (one-off CPU work in the reference too).  seed == 0 draws from the OS. */
+typedef struct fhs_client_key fhs_client_key;
+int fhs_generate_keys(const fhs_params *params /* NULL: PARAM_MESSAGE_2_CARRY_2_KS_PBS */,
+                      const double *stds /* {lwe_std, glwe_std} or NULL */, size_t l, uint64_t seed,
+                      fhs_client_key **out);
+void fhs_client_key_destroy(fhs_client_key *k);
+const char *fhs_client_last_error(void);
+int fhs_client_key_info(const fhs_client_key *k, fhs_params *p, uint32_t *num_blocks_char,
+                        uint32_t *num_blocks_usize, size_t *max_len);
+/* Server key material in the layouts fhs_upload_keys takes (KSK level order MSB first). */
+const uint64_t *fhs_client_ksk(const fhs_client_key *k, size_t *len);
+const uint64_t *fhs_client_bsk(const fhs_client_key *k, size_t *len);
+int fhs_encrypt_blocks(fhs_client_key *k, const uint64_t *msgs, size_t n, uint64_t *out);
+int fhs_decrypt_blocks(const fhs_client_key *k, const uint64_t *cts, size_t n, uint64_t *msgs_out);
+/* FheString::new validation + layout: same five error messages as mod.rs:59-71. */
+int fhs_string_layout(const fhs_client_key *k, const char *s, int64_t pad, uint64_t *block_values,
+                      size_t cap_blocks, size_t *n_chars);
+
 #ifdef __cplusplus
 }
 #endif

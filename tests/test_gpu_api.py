@@ -1,0 +1,39 @@
+"""GPU: the product's own client (keygen / encrypt / decrypt) + server API, no oracle involved."""
+import subprocess
+import sys
+import os
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def keys():
+    from fhe_string_b200.api import generate_keys
+    return generate_keys(l=255, seed=11)
+
+
+def test_api_roundtrip_and_ops(keys):
+    ck, sk = keys
+    s = ck.encrypt_str("Hello, B200!", 16)
+    p = ck.encrypt_str("B2")
+    assert s.decrypt(ck) == "Hello, B200!"
+    assert s.contains(sk, p).decrypt(ck) is True
+    assert s.find(sk, p).decrypt(ck) == 7
+    assert s.to_uppercase(sk).decrypt(ck) == "HELLO, B200!"
+    assert s.len(sk).decrypt(ck) == 12
+    assert s.split(sk, ck.encrypt_str("l")).decrypt(ck) == "Hello, B200!".split("l")
+    assert s.replace(sk, ck.encrypt_str("l"), ck.encrypt_str("LL"), 14).decrypt(ck) == "HeLLLLo, B200!"
+    assert s.strip_prefix(sk, ck.encrypt_str("Hello")).decrypt(ck) == ", B200!"
+    assert s.strip_prefix(sk, p).decrypt(ck) is None
+    assert s.substr_from(sk, ck.encrypt_usize(7)).decrypt(ck) == "B200!"
+
+
+def test_cmd_driver_all_equal():
+    """BASELINE configs[0]: examples/cmd --input " A bcbc " --pattern "bc"."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "cmd.py"), "--input", " A bcbc ",
+                        "--pattern", "bc", "--seed", "3"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "❌" not in r.stdout and "all equal: True" in r.stdout
