@@ -357,7 +357,9 @@ __global__ void __launch_bounds__(kThreads2, 1)
 blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__restrict__ lut_id,
                        const uint64_t *__restrict__ lut_tables, const double2 *__restrict__ bsk_f,
                        const double2 *__restrict__ twiddle_g, uint64_t *__restrict__ lwe_out,
-                       unsigned int batch, int n_lwe, int log_box, uint64_t delta) {
+                       unsigned int batch, int n_lwe, int log_box, uint64_t delta, int active_slots) {
+    // active_slots in {1, 2, 4}: small levels use fewer ciphertexts per CTA (more CTAs, shorter
+    // iterations); idle compute / loader warps skip the main loops entirely.
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem2 &sm = *reinterpret_cast<Smem2 *>(smem_raw);
     const int warp = threadIdx.x >> 5;
@@ -369,16 +371,19 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
     __syncthreads();
     tmem_fence_after_sync();
     const uint32_t tbase = sm.tmem_base + (((uint32_t)(warp & 3) * 32u) << 16);
-    const unsigned int n_groups = (batch + kSlots2 - 1) / kSlots2;
+    const unsigned int n_groups = (batch + active_slots - 1) / active_slots;
+    const int active_loaders = active_slots == 1 ? 2 : 4;
+    const int bar_threads = 64 * active_slots + 32 * active_loaders;
 
     if (warp >= 2 * kSlots2) {
+        const bool loader_active = (warp & 3) < active_loaders;
         // =========================== BSK loader warps ===========================
         // Register budget: the pool that setmaxnreg.inc draws from is what the loaders release, so
         // (R_compute - 168) * 256 <= (168 - R_loader) * 128  ->  56 / 224.
         asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
         const int role = warp & 1;  // lane quarter q = warp & 3 serves compute warps with w = q & 1
         bool first = true;
-        for (unsigned int g = blockIdx.x; g < n_groups; g += gridDim.x) {
+        for (unsigned int g = blockIdx.x; loader_active && g < n_groups; g += gridDim.x) {
             for (int i = 0; i < n_lwe; i++) {
                 const uint4 *__restrict__ src = reinterpret_cast<const uint4 *>(
                     bsk_f + ((((size_t)i * 32) * 2 + role) * 32 + lane) * 2);
@@ -392,7 +397,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         ldg_b128(p + 1, r[8 * k + 4], r[8 * k + 5], r[8 * k + 6], r[8 * k + 7]);
                     }
                     if (b == 0 && !first) {     // previous slice fully consumed?
-                        named_bar_sync(kBarFree, kThreads2);
+                        named_bar_sync(kBarFree, bar_threads);
                         tmem_fence_after_sync();
                     }
                     tmem_st32(tbase + kTmemBskCol + 32 * b, r);
@@ -400,7 +405,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 first = false;
                 tmem_wait_st();
                 tmem_fence_before_sync();
-                named_bar_arrive(kBarFull, kThreads2);
+                named_bar_arrive(kBarFull, bar_threads);
             }
         }
     } else {
@@ -417,8 +422,8 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
         const uint32_t tbsk = tbase + kTmemBskCol;
         const unsigned int last_group = ((n_groups - 1 - blockIdx.x) / gridDim.x) * gridDim.x + blockIdx.x;
 
-        for (unsigned int g = blockIdx.x; g < n_groups; g += gridDim.x) {
-            unsigned int ct = g * kSlots2 + slot;
+        for (unsigned int g = blockIdx.x; slot < active_slots && g < n_groups; g += gridDim.x) {
+            unsigned int ct = g * active_slots + slot;
             if (ct >= batch) ct = batch - 1;  // idle slot of the last group: recompute the last one
             const uint64_t *__restrict__ lwe = lwe_small + (size_t)ct * (n_lwe + 1);
             for (int t = threadIdx.x & 63; t < n_lwe; t += 64) ss.amod[t] = (uint16_t)modswitch(lwe[t]);
@@ -489,7 +494,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 }
                 fft32_pos(xr, xi);
                 // ---- GGSW contraction against the BSK slice parked in TMEM ----
-                named_bar_sync(kBarFull, kThreads2);
+                named_bar_sync(kBarFull, bar_threads);
                 tmem_fence_after_sync();
 #pragma unroll
                 for (int b = 0; b < 8; b++) {
@@ -514,7 +519,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 }
                 if (!(g == last_group && i == n_lwe - 1)) {
                     tmem_fence_before_sync();
-                    named_bar_arrive(kBarFree, kThreads2);
+                    named_bar_arrive(kBarFree, bar_threads);
                 }
 #pragma unroll
                 for (int q = 0; q < 32; q++) {
@@ -728,11 +733,12 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
             d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, c->d_counter,
             (unsigned int)batch, (int)c->n, log_box, delta);
     } else {
-        size_t ctas = (batch + kSlots2 - 1) / kSlots2;
+        const int active = batch <= (size_t)c->sm_count ? 1 : (batch <= 2 * (size_t)c->sm_count ? 2 : kSlots2);
+        size_t ctas = (batch + active - 1) / active;
         if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
         blind_rotate_v2_kernel<<<(unsigned)ctas, kThreads2, sizeof(Smem2), c->stream>>>(
             d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, (unsigned int)batch,
-            (int)c->n, log_box, delta);
+            (int)c->n, log_box, delta, active);
     }
     c->launches++;
     FHS_CUDA(cudaGetLastError());

@@ -42,7 +42,11 @@ keyswitch_kernel(const uint64_t *__restrict__ in, const uint64_t *__restrict__ k
                  const uint64_t *__restrict__ corr, uint64_t *__restrict__ out, unsigned int batch,
                  int n_small, int big, int cts_per_cta) {
     __shared__ __align__(16) uint32_t dig[kKsIc][kKsLevels][TB];
+    // blockIdx.y = slice of the mask range (split-K for small batches: more CTAs stream the KSK)
     const int t = threadIdx.x;
+    const int ksplit = gridDim.y;
+    const int ic_begin = (int)((long long)big * blockIdx.y / ksplit);
+    const int ic_end = (int)((long long)big * (blockIdx.y + 1) / ksplit);
     const unsigned int c0 = blockIdx.x * cts_per_cta;
     const int nb = (int)min((unsigned int)cts_per_cta, batch - c0);
     const int out_w = n_small + 1;
@@ -58,7 +62,7 @@ keyswitch_kernel(const uint64_t *__restrict__ in, const uint64_t *__restrict__ k
 #pragma unroll
     for (int c = 0; c < kKsCols; c++) col_ok[c] = (t + c * kKsThreads) < out_w;
 
-    for (int ic = 0; ic < big; ic += kKsIc) {
+    for (int ic = ic_begin; ic < ic_end; ic += kKsIc) {
         // ---- stage digits of mask elements [ic, ic+16) for the tile's ciphertexts ----
         for (int p = t; p < kKsIc * TB; p += kKsThreads) {
             const int b = p / kKsIc, ii = p % kKsIc;
@@ -109,7 +113,13 @@ keyswitch_kernel(const uint64_t *__restrict__ in, const uint64_t *__restrict__ k
             for (int b = 0; b < TB; b++) {
                 if (b < nb) {
                     const uint64_t body = (j == n_small) ? in[(size_t)(c0 + b) * in_w + big] : 0ull;
-                    out[(size_t)(c0 + b) * out_w + j] = body - (acc[b][c] - cr);
+                    if (ksplit == 1) {
+                        out[(size_t)(c0 + b) * out_w + j] = body - (acc[b][c] - cr);
+                    } else {  // out was zeroed by the launcher; slice 0 also carries body and offset
+                        const uint64_t v = (blockIdx.y == 0 ? body + cr : 0ull) - acc[b][c];
+                        atomicAdd(reinterpret_cast<unsigned long long *>(out + (size_t)(c0 + b) * out_w + j),
+                                  (unsigned long long)v);
+                    }
                 }
             }
         }
@@ -168,7 +178,12 @@ int launch_keyswitch(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_sma
     int per = (int)((batch + c->sm_count - 1) / c->sm_count);
     if (per < 1) per = 1;
     if (per > kKsTb) per = kKsTb;
-    const unsigned grid = (unsigned)((batch + per - 1) / per);
+    const unsigned tiles = (unsigned)((batch + per - 1) / per);
+    unsigned ksplit = 1;
+    while (ksplit < 32 && tiles * ksplit * 2 <= (unsigned)c->sm_count) ksplit *= 2;
+    if (ksplit > 1)
+        FHS_CUDA(cudaMemsetAsync(d_small, 0, batch * ((size_t)c->n + 1) * sizeof(uint64_t), c->stream));
+    const dim3 grid(tiles, ksplit);
     if (per <= 4)
         keyswitch_kernel<4><<<grid, kKsThreads, 0, c->stream>>>(
             d_in, c->d_ksk, c->d_ksk_corr, d_small, (unsigned int)batch, (int)c->n, (int)c->big, per);
