@@ -57,6 +57,15 @@ def synth_inputs(ks, batch, seed):
     return msgs, cts, lut_id
 
 
+def synth_inputs_product(ck, batch, seed):
+    """Synthetic encrypted blocks made with the product's client key (fhs_encrypt_blocks)."""
+    rng = np.random.default_rng(seed)
+    msgs = rng.integers(0, 16, batch)
+    cts = ck.encrypt_blocks(msgs.astype(np.uint64))
+    lut_id = (np.arange(batch) % 8).astype(np.uint32)
+    return msgs, cts, lut_id
+
+
 class ClockSampler:
     def __init__(self, gpu_index):
         self.gpu = gpu_index
@@ -96,6 +105,31 @@ class ClockSampler:
         med = float(np.median(self.samples)) if self.samples else None
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
                 "samples": len(self.samples)}
+
+
+def string_op_latency(ck, eng):
+    """BASELINE configs[2]: eq / contains / find (+ split) on a 64-char padded encrypted string with
+    an 8-char encrypted pattern; wall-clock per call through the public API (median of 3),
+    host<->device copies of the operand / result blocks included."""
+    from fhe_string_b200.api import ServerKey
+    sk = ServerKey(ck, engine=eng)
+    rng = np.random.default_rng(7)
+    s = "".join(chr(int(c)) for c in rng.integers(33, 127, 40))
+    pat = s[13:21]
+    es, ep = ck.encrypt_str(s, 64), ck.encrypt_str(pat)
+    res = {}
+    for name, call, want in (("eq", lambda: es.eq(sk, es), True), ("contains", lambda: es.contains(sk, ep), True),
+                             ("find", lambda: es.find(sk, ep), 13), ("split", lambda: es.split(sk, ep), s.split(pat))):
+        ts = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            r = call()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        st = sk.last_stats
+        res[name] = {"ms": float(np.median(ts)), "lut_evals": st["pbs"], "levels": st["levels"],
+                     "correct": r.decrypt(ck) == want}
+    res["config"] = "64-char padded string (40 chars), 8-char pattern, 1 GPU"
+    return res
 
 
 def cpu_baseline(ks, tables, threads, target_seconds=12.0):
@@ -167,7 +201,7 @@ def main():
 
     import torch
     import fhe_string_b200 as F
-    from oracle import oracle as O   # key generation + the cpu_baseline leg only
+    from fhe_string_b200.api import ClientKey   # product client: keygen / encrypt / decrypt (CPU)
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -183,12 +217,12 @@ def main():
     batch = args.batch
 
     # ---- keys: rank 0 generates (client side, CPU), broadcast over NCCL, upload per GPU ----
-    ks = O.Keyset(seed=1)            # deterministic: every rank could regenerate, but the product
-    p = ks.p                         # path is "broadcast keys over NVLink" (north_star)
+    ck = ClientKey(l=255, seed=1)    # deterministic: every rank could regenerate, but the product
+    p = ck.p                         # path is "broadcast keys over NVLink" (north_star)
     if world > 1:
         if rank == 0:
-            ksk_t = torch.from_numpy(ks.ksk().view(np.int64)).to(dev)
-            bsk_t = torch.from_numpy(ks.bsk().view(np.int64)).to(dev)
+            ksk_t = torch.from_numpy(ck.ksk().view(np.int64).copy()).to(dev)
+            bsk_t = torch.from_numpy(ck.bsk().view(np.int64).copy()).to(dev)
         else:
             ksk_t = torch.empty(p.glwe_dim * p.poly_size * p.ks_level * (p.lwe_dim + 1), dtype=torch.int64, device=dev)
             bsk_t = torch.empty(p.lwe_dim * 4 * p.poly_size, dtype=torch.int64, device=dev)
@@ -198,7 +232,7 @@ def main():
         bsk = bsk_t.cpu().numpy().view(np.uint64)
         del ksk_t, bsk_t
     else:
-        ksk, bsk = ks.ksk(), ks.bsk()
+        ksk, bsk = ck.ksk(), ck.bsk()
     eng = F.Engine(local)
     eng.upload_keys(p, ksk, bsk, ksk_level_order=0)
     # a non-default torch stream: its handle is non-NULL, so the library launches on exactly the
@@ -213,7 +247,7 @@ def main():
     nbuf = 3
     host_in, dev_in, msgs_l = [], [], []
     for b in range(nbuf):
-        msgs, cts, lut_id = synth_inputs(ks, batch, seed=1000 * (rank + 1) + b)
+        msgs, cts, lut_id = synth_inputs_product(ck, batch, seed=1000 * (rank + 1) + b)
         hp = torch.from_numpy(cts.view(np.int64)).pin_memory()
         host_in.append(hp)
         dev_in.append(hp.to(dev, non_blocking=True))
@@ -270,7 +304,7 @@ def main():
     torch.cuda.synchronize()
     last = (min(args.steps, 5) - 1) % nbuf
     out_np = d_out.cpu().numpy().view(np.uint64)
-    ok_dev = bool(np.array_equal(ks.decrypt(out_np), tables[lut_id, msgs_l[last]]))
+    ok_dev = bool(np.array_equal(ck.decrypt_blocks(out_np), tables[lut_id, msgs_l[last]]))
 
     # ---- end-to-end timing through the host-buffer C ABI ----
     for i in range(warm):
@@ -285,7 +319,7 @@ def main():
     barrier()
     e2e_ms = t_e2e0.elapsed_time(t_e2e1)
     out_np = host_out.numpy().view(np.uint64)
-    ok_e2e = bool(np.array_equal(ks.decrypt(out_np), tables[lut_id, msgs_l[(args.steps - 1) % nbuf]]))
+    ok_e2e = bool(np.array_equal(ck.decrypt_blocks(out_np), tables[lut_id, msgs_l[(args.steps - 1) % nbuf]]))
 
     # ---- max over ranks ----
     if dist is not None:
@@ -341,8 +375,11 @@ def main():
                     "ms_per_step": e2e_ms / args.steps},
             "clocks": clocks,
         }
+        if world == 1:
+            line["op_latency"] = string_op_latency(ck, eng)
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(ks, tables, 0)
+            from oracle import oracle as O      # the cpu_baseline leg: the only use of oracle/ here
+            line["cpu_baseline"] = cpu_baseline(O.Keyset(seed=1), tables, 0)
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line), flush=True)

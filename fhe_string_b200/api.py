@@ -120,9 +120,11 @@ class ClientKey:
 class ServerKey:
     """src/server_key.rs:12-33: key material on the GPU + program cache."""
 
-    def __init__(self, ck, device=0):
-        self.engine = Engine(device)
-        self.engine.upload_keys(ck.p, ck.ksk(), ck.bsk(), ksk_level_order=0)
+    def __init__(self, ck, device=0, engine=None):
+        if engine is None:
+            engine = Engine(device)
+            engine.upload_keys(ck.p, ck.ksk(), ck.bsk(), ksk_level_order=0)
+        self.engine = engine
         self.num_blocks_char, self.num_blocks_usize = ck.num_blocks_char, ck.num_blocks_usize
         self.max_len = ck.max_len
         self._progs = {}
