@@ -57,6 +57,8 @@ static int ensure_capacity(Ctx *c, size_t batch, size_t n_luts) {
 static void free_keys(Ctx *c) {
     cudaFree(c->d_ksk);
     cudaFree(c->d_ksk_corr);
+    cudaFree(c->d_ksk_t);
+    c->d_ksk_t = nullptr;
     cudaFree(c->d_bsk_f);
     c->d_ksk = c->d_ksk_corr = nullptr;
     c->d_bsk_f = nullptr;
@@ -220,6 +222,7 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
         cudaError_t e;
         if ((e = cudaMalloc(&c->d_ksk, ksk_len * sizeof(uint64_t))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_ksk_corr, (c->n + 1) * sizeof(uint64_t))) != cudaSuccess ||
+            (e = cudaMalloc(&c->d_ksk_t, fhs::ksk_tiles_bytes(c))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_bsk_f, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "cudaMalloc(keys)");
             break;
@@ -230,6 +233,7 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
             break;
         }
         if ((rc = fhs::launch_ksk_prepare(c, d_raw, ksk_level_order)) != FHS_OK) break;
+        if ((rc = fhs::launch_ksk_tile(c)) != FHS_OK) break;
         if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "ksk prepare");
             break;

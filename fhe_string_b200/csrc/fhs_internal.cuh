@@ -24,6 +24,7 @@ struct Ctx {
     uint32_t space = 0;            // message_modulus * carry_modulus
     // device key material
     uint64_t *d_ksk = nullptr;     // [k*N][ks_level (digit order, least significant first)][n+1]
+    uint8_t *d_ksk_t = nullptr;    // byte-limb tiles of the KSK for the tensor-core keyswitch
     uint64_t *d_ksk_corr = nullptr;// [n+1]  2^(base_log-1) * sum of all KSK rows (unsigned-digit offset)
     double2 *d_bsk_f = nullptr;    // Fourier BSK, layout in blind_rotate.cu
     double2 *d_twiddle = nullptr;  // [32][33] inter-pass twiddles T[k2][n1]
@@ -53,6 +54,10 @@ int cuda_fail(cudaError_t e, const char *what);
 // keyswitch.cu
 int launch_keyswitch(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_small);
 int launch_ksk_prepare(Ctx *c, const uint64_t *d_ksk_raw, int level_order);
+// keyswitch_mma.cu
+size_t ksk_tiles_bytes(const Ctx *c);
+int launch_ksk_tile(Ctx *c);
+int launch_keyswitch_mma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_small);
 // blind_rotate.cu
 int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                         const uint64_t *d_tables, size_t batch, uint64_t *d_out);

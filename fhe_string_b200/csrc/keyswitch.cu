@@ -7,6 +7,8 @@
 // one KSK pass serves kKsTb ciphertexts.  Digits are offset to [0, 2^base_log] so each MAC is
 // IMAD.WIDE.U32 + IMAD; the offset is removed with a per-column constant computed at upload.
 // Integer arithmetic only: bit-exact against the oracle.
+#include <cstdlib>
+
 #include "fhs_internal.cuh"
 
 namespace fhs {
@@ -174,6 +176,10 @@ int launch_keyswitch(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_sma
         set_error("keyswitch kernel built for ks_base_log=3, ks_level=5, n+1<=768");
         return FHS_ERR_INVALID;
     }
+    // large levels: integer tensor cores (keyswitch_mma.cu); FHS_KS_VARIANT=1 forces the IMAD kernel
+    static int variant = -1;
+    if (variant < 0) { const char *e = getenv("FHS_KS_VARIANT"); variant = e ? atoi(e) : 2; }
+    if (variant == 2 && batch >= 24) return launch_keyswitch_mma(c, d_in, batch, d_small);
     // tile size: fill the SMs first, then grow tiles up to kKsTb (KSK traffic ~ 1/tile)
     int per = (int)((batch + c->sm_count - 1) / c->sm_count);
     if (per < 1) per = 1;
