@@ -110,192 +110,6 @@ __device__ __forceinline__ void fwd_cols(double (&xr)[32], double (&xi)[32],
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
-blind_rotate_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__restrict__ lut_id,
-                    const uint64_t *__restrict__ lut_tables, const double2 *__restrict__ bsk_f,
-                    const double2 *__restrict__ twiddle_g, uint64_t *__restrict__ lwe_out,
-                    unsigned int *__restrict__ counter, unsigned int batch, int n_lwe, int log_box,
-                    uint64_t delta) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
-    const int slot = threadIdx.x >> 6;
-    const int w = (threadIdx.x >> 5) & 1;
-    const int lane = threadIdx.x & 31;
-    SlotSmem &ss = sm.slot[slot];
-    const int table_len = kN >> log_box;
-
-    for (int t = threadIdx.x; t < kTile; t += kThreads) sm.T[t] = twiddle_g[t];
-    __syncthreads();
-
-    // row-pass role of this thread
-    const int rp = lane >> 4;                  // polynomial handled in the row passes
-    const int rk2 = 16 * w + (lane & 15);      // frequency residue k2 handled in the row passes
-    uint64_t *__restrict__ P = ss.acc[w];
-
-    for (;;) {
-        if ((threadIdx.x & 63) == 0) ss.cur = atomicAdd(counter, 1u);
-        slot_bar(slot);
-        const unsigned int ct = ss.cur;
-        if (ct >= batch) break;
-        const uint64_t *__restrict__ lwe = lwe_small + (size_t)ct * (n_lwe + 1);
-        for (int t = threadIdx.x & 63; t < n_lwe; t += 64) ss.amod[t] = (uint16_t)modswitch(lwe[t]);
-        const uint32_t bt = modswitch(lwe[n_lwe]);
-        if (w == 0) {
-#pragma unroll 8
-            for (int m = 0; m < kN / 32; m++) P[lane + 32 * m] = 0ull;
-        } else {
-            const uint64_t *__restrict__ tab = lut_tables + (size_t)lut_id[ct] * table_len;
-#pragma unroll 8
-            for (int m = 0; m < kN / 32; m++)
-                P[lane + 32 * m] = lut_coeff(tab, lane + 32 * m, bt, log_box, delta);
-        }
-        slot_bar(slot);
-
-        for (int i = 0; i < n_lwe; i++) {
-            const uint32_t a = ss.amod[i];
-            if (a == 0) continue;  // uniform over the slot's 64 threads
-
-            double xr[32], xi[32];
-            // ---- (X^a - 1) * acc_w, signed digit, pre-twist: inputs of the column pass ----
-            {
-                const uint32_t base = (uint32_t)(lane - (int)a) & (2 * kN - 1);
-#pragma unroll
-                for (int m = 0; m < 32; m++) {
-                    const uint32_t idx0 = (base + 32 * m) & (2 * kN - 1);
-                    const uint32_t idx1 = (idx0 + kH) & (2 * kN - 1);
-                    const uint64_t own0 = P[lane + 32 * m];
-                    const uint64_t own1 = P[lane + 32 * m + kH];
-                    const uint64_t r0 = P[idx0 & (kN - 1)];
-                    const uint64_t r1 = P[idx1 & (kN - 1)];
-                    const uint64_t m0 = (idx0 & kN) ? ~0ull : 0ull;
-                    const uint64_t m1 = (idx1 & kN) ? ~0ull : 0ull;
-                    const double d0 = int_to_double(pbs_digit((r0 ^ m0) - m0 - own0));
-                    const double d1 = int_to_double(pbs_digit((r1 ^ m1) - m1 - own1));
-                    if (m == 0) {
-                        xr[FHS_BR5(m)] = d0;
-                        xi[FHS_BR5(m)] = d1;
-                    } else {
-                        xr[FHS_BR5(m)] = d0 * kPreRe[m] - d1 * kPreIm[m];
-                        xi[FHS_BR5(m)] = d0 * kPreIm[m] + d1 * kPreRe[m];
-                    }
-                }
-            }
-            fwd_cols(xr, xi, sm.T, lane);
-            // ---- transpose: S[w][k2][n1 = lane] ----
-            __syncwarp();  // this warp's inverse-pass reads of plane w (previous iteration) are done
-            {
-                double2 *__restrict__ Sw = ss.S[w];
-#pragma unroll
-                for (int k2 = 0; k2 < 32; k2++) Sw[k2 * kTStride + lane] = make_double2(xr[k2], xi[k2]);
-            }
-            // BSK prefetch ring: the first kBskRing frequency rows are requested before the
-            // barrier and the row pass so their L2 latency is hidden behind the transpose + DFT-32.
-            const double2 *__restrict__ Bp = bsk_f + ((((size_t)i * 32) * 2 + w) * 32 + lane) * 2;
-            double2 bs[kBskRing], bk[kBskRing];
-#pragma unroll
-            for (int q = 0; q < kBskRing; q++) {
-                bs[q] = ldg_stream(Bp + (size_t)q * 128);      // GGSW row rp, column 1 - rp
-                bk[q] = ldg_stream(Bp + (size_t)q * 128 + 1);  // GGSW row rp, column rp
-            }
-            slot_bar(slot);
-            {
-                const double2 *__restrict__ Sr = ss.S[rp] + rk2 * kTStride;
-#pragma unroll
-                for (int n1 = 0; n1 < 32; n1++) {
-                    const double2 v = Sr[n1];
-                    xr[FHS_BR5(n1)] = v.x;
-                    xi[FHS_BR5(n1)] = v.y;
-                }
-            }
-            fft32_pos(xr, xi);  // slot k1: D_rp[32 k1 + rk2]
-            // ---- GGSW contraction: F_c = D_0 B[0][c] + D_1 B[1][c] ----
-            // Result for frequency row k1 goes to slot BR5(k1) (input order of the inverse DFT-32):
-            // rows are visited so that a slot is overwritten only after its own row was consumed.
-            {
-#pragma unroll
-                for (int k1 = 0; k1 < 32; k1++) {
-                    const double2 cs = bs[k1 % kBskRing], ck = bk[k1 % kBskRing];
-                    if (k1 + kBskRing < 32) {
-                        bs[k1 % kBskRing] = ldg_stream(Bp + (size_t)(k1 + kBskRing) * 128);
-                        bk[k1 % kBskRing] = ldg_stream(Bp + (size_t)(k1 + kBskRing) * 128 + 1);
-                    }
-                    const double dr = xr[k1], di = xi[k1];
-                    const double sr = dr * cs.x - di * cs.y;
-                    const double si = dr * cs.y + di * cs.x;
-                    const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
-                    const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
-                    xr[k1] = fma(dr, ck.x, fma(-di, ck.y, gr));
-                    xi[k1] = fma(dr, ck.y, fma(di, ck.x, gi));
-                }
-                // bit-reversal permutation of the 32 slots (register renaming only)
-#pragma unroll
-                for (int q = 0; q < 32; q++) {
-                    if (FHS_BR5(q) > q) {
-                        double t0 = xr[q]; xr[q] = xr[FHS_BR5(q)]; xr[FHS_BR5(q)] = t0;
-                        double t1 = xi[q]; xi[q] = xi[FHS_BR5(q)]; xi[FHS_BR5(q)] = t1;
-                    }
-                }
-            }
-            // ---- inverse row pass (over k1 -> n1), conjugate twiddle ----
-            fft32_neg(xr, xi);
-            {
-                const double2 *__restrict__ Tr = sm.T + rk2 * kTStride;
-#pragma unroll
-                for (int n1 = 0; n1 < 32; n1++) {
-                    const double2 t = Tr[n1];
-                    const double a0 = xr[n1], b0 = xi[n1];
-                    xr[n1] = a0 * t.x + b0 * t.y;
-                    xi[n1] = b0 * t.x - a0 * t.y;
-                }
-            }
-            __syncwarp();  // forward-pass reads of these rows (by this warp) are done
-            {
-                double2 *__restrict__ Sq = ss.S[rp] + rk2 * kTStride;
-#pragma unroll
-                for (int n1 = 0; n1 < 32; n1++) Sq[n1] = make_double2(xr[n1], xi[n1]);
-            }
-            slot_bar(slot);
-            {
-                const double2 *__restrict__ Sw = ss.S[w];
-#pragma unroll
-                for (int k2 = 0; k2 < 32; k2++) {
-                    const double2 v = Sw[k2 * kTStride + lane];
-                    xr[FHS_BR5(k2)] = v.x;
-                    xi[FHS_BR5(k2)] = v.y;
-                }
-            }
-            // ---- inverse column pass (over k2 -> n2), conjugate pre-twist, add as torus ----
-            fft32_neg(xr, xi);
-#pragma unroll
-            for (int m = 0; m < 32; m++) {
-                double ur, ui;
-                if (m == 0) {
-                    ur = xr[m];
-                    ui = xi[m];
-                } else {
-                    ur = xr[m] * kPreRe[m] + xi[m] * kPreIm[m];
-                    ui = xi[m] * kPreRe[m] - xr[m] * kPreIm[m];
-                }
-                P[lane + 32 * m] += f64_to_torus(ur);
-                P[lane + 32 * m + kH] += f64_to_torus(ui);
-            }
-            __syncwarp();  // accumulator updates visible to this warp's rotated reads
-        }
-
-        // ---- a1.7 sample extract at coefficient 0 ----
-        uint64_t *__restrict__ out = lwe_out + (size_t)ct * (kN + 1);
-        if (w == 0) {
-#pragma unroll 8
-            for (int m = 0; m < kN / 32; m++) {
-                const int j = lane + 32 * m;
-                out[j] = (j == 0) ? P[0] : (0ull - P[kN - j]);
-            }
-        } else if (lane == 0) {
-            out[kN] = P[0];
-        }
-    }
-}
-
 // =================================================================================================
 // v2: "lock-step CTA with TMEM": 4 ciphertext slots (8 compute warps) + 4 loader warps per CTA.
 //   * The accumulator lives in Tensor Memory: every compute thread owns 64 coefficients of its
@@ -418,7 +232,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
         const int rp = lane >> 4;
         const int rk2 = 16 * w + (lane & 15);
         uint32_t *__restrict__ H = ss.hi[w];
-        const uint32_t tacc = tbase + (uint32_t)(warp >> 2) * 128u;  // hi words [0,64), lo words [64,128)
+        const uint32_t tacc = tbase + (uint32_t)(warp >> 2) * 128u;  // 64 columns: high words of 64 coefficients
         const uint32_t tbsk = tbase + kTmemBskCol;
         const unsigned int last_group = ((n_groups - 1 - blockIdx.x) / gridDim.x) * gridDim.x + blockIdx.x;
 
@@ -431,17 +245,15 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 // a1.1 + rotation by X^{-b~}: this thread's 64 coefficients -> TMEM + hi plane
                 const uint32_t bt = modswitch(lwe[n_lwe]);
                 const uint64_t *__restrict__ tab = lut_tables + (size_t)lut_id[ct] * table_len;
-                uint32_t vhi[64], vlo[64];
+                uint32_t vhi[64];
 #pragma unroll
                 for (int q = 0; q < 64; q++) {
                     const int j = lane + 32 * (q >> 1) + kH * (q & 1);
                     const uint64_t v = (w == 0) ? 0ull : lut_coeff(tab, (uint32_t)j, bt, log_box, delta);
-                    vhi[q] = (uint32_t)(v >> 32);
-                    vlo[q] = (uint32_t)v;
+                    vhi[q] = (uint32_t)(v >> 32);   // low words of f * Delta are zero
                     H[j] = vhi[q];
                 }
                 tmem_st64(tacc, vhi);
-                tmem_st64(tacc + 64, vlo);
                 tmem_wait_st();
             }
             slot_bar(slot);  // amod + hi plane visible
@@ -559,9 +371,8 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 // ---- conjugate pre-twist, add as torus into the TMEM accumulator ----
 #pragma unroll
                 for (int c = 0; c < 4; c++) {   // 8 values of m (16 coefficients) per chunk
-                    uint32_t ohi[16], olo[16];
+                    uint32_t ohi[16];
                     tmem_ld16(tacc + 16 * c, ohi);
-                    tmem_ld16(tacc + 64 + 16 * c, olo);
                     tmem_wait_ld();
 #pragma unroll
                     for (int mm = 0; mm < 8; mm++) {
@@ -574,17 +385,14 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                             ur = xr[m] * fhs_pre_re(m) + xi[m] * fhs_pre_im(m);
                             ui = xi[m] * fhs_pre_re(m) - xr[m] * fhs_pre_im(m);
                         }
-                        const uint64_t n0 = (((uint64_t)ohi[2 * mm] << 32) | olo[2 * mm]) + f64_to_torus(ur);
-                        const uint64_t n1v = (((uint64_t)ohi[2 * mm + 1] << 32) | olo[2 * mm + 1]) + f64_to_torus(ui);
-                        ohi[2 * mm] = (uint32_t)(n0 >> 32);
-                        olo[2 * mm] = (uint32_t)n0;
-                        ohi[2 * mm + 1] = (uint32_t)(n1v >> 32);
-                        olo[2 * mm + 1] = (uint32_t)n1v;
+                        // values arrive in units of 2^34 (scale folded into the Fourier BSK):
+                        // hi word += (round(v / 2^34) << 2) mod 2^32
+                        ohi[2 * mm] += (uint32_t)__double2ll_rn(ur) << 2;
+                        ohi[2 * mm + 1] += (uint32_t)__double2ll_rn(ui) << 2;
                         H[lane + 32 * m] = ohi[2 * mm];
                         H[lane + 32 * m + kH] = ohi[2 * mm + 1];
                     }
                     tmem_st16(tacc + 16 * c, ohi);
-                    tmem_st16(tacc + 64 + 16 * c, olo);
                 }
                 tmem_wait_st();
                 __syncwarp();  // hi plane of polynomial w complete before this warp's rotated reads
@@ -592,9 +400,8 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
 
             // ---- a1.7 sample extract at coefficient 0, from the TMEM accumulator ----
             {
-                uint32_t vhi[64], vlo[64];
+                uint32_t vhi[64];
                 tmem_ld64(tacc, vhi);
-                tmem_ld64(tacc + 64, vlo);
                 tmem_wait_ld();
                 uint64_t *__restrict__ out = lwe_out + (size_t)ct * (kN + 1);
                 if (w == 0) {
@@ -602,12 +409,12 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
 #pragma unroll
                     for (int q = 0; q < 64; q++) {
                         const int cidx = lane + 32 * (q >> 1) + kH * (q & 1);
-                        const uint64_t v = ((uint64_t)vhi[q] << 32) | vlo[q];
+                        const uint64_t v = (uint64_t)vhi[q] << 32;
                         if (cidx == 0) out[0] = v;
                         else out[kN - cidx] = 0ull - v;
                     }
                 } else if (lane == 0) {
-                    out[kN] = ((uint64_t)vhi[0] << 32) | vlo[0];
+                    out[kN] = (uint64_t)vhi[0] << 32;
                 }
             }
             slot_bar(slot);  // amod / hi plane reuse by the next group
@@ -662,7 +469,7 @@ bsk_transform_kernel(const uint64_t *__restrict__ bsk, double2 *__restrict__ bsk
     fft32_pos(xr, xi);
     const int k2 = lane;
     const int ww = k2 >> 4, lp = (r << 4) | (k2 & 15), sl = (c == r) ? 1 : 0;
-    const double sc = 1.0 / 1024.0;
+    const double sc = 1.0 / 1024.0 / 17179869184.0;  // 1/1024 (inverse FFT) and 2^-34 (accumulator unit)
 #pragma unroll
     for (int k1 = 0; k1 < 32; k1++) {
         bsk_f[((((size_t)i * 32 + k1) * 2 + ww) * 32 + lp) * 2 + sl] =
@@ -712,27 +519,16 @@ int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc) {
 int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                         const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
-    static int variant = -1;
-    if (variant < 0) {
-        const char *e = getenv("FHS_BR_VARIANT");
-        variant = e ? atoi(e) : 2;
-        FHS_CUDA(cudaFuncSetAttribute(blind_rotate_kernel,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(Smem)));
+    static bool attr_set = false;
+    if (!attr_set) {
         FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(Smem2)));
+        attr_set = true;
     }
     const int log_box = ilog2(kN / c->space);
     const uint64_t delta = (1ull << 63) / c->space;
-    if (variant == 1) {
-        FHS_CUDA(cudaMemsetAsync(c->d_counter, 0, sizeof(unsigned int), c->stream));
-        size_t ctas = (batch + kCtPerCta - 1) / kCtPerCta;
-        if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
-        blind_rotate_kernel<<<(unsigned)ctas, kThreads, sizeof(Smem), c->stream>>>(
-            d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, c->d_counter,
-            (unsigned int)batch, (int)c->n, log_box, delta);
-    } else {
+    {
         const int active = batch <= (size_t)c->sm_count ? 1 : (batch <= 2 * (size_t)c->sm_count ? 2 : kSlots2);
         size_t ctas = (batch + active - 1) / active;
         if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
