@@ -197,9 +197,46 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
 // Executor: level by level on a device-resident pool (fhs_pool / fhs_level of include/fhs_cuda.h).
 #include <chrono>
 
+// Slice of a level of B evaluations owned by `rank`: levels below shard_min * world evaluations are
+// computed redundantly by every rank (one blind-rotation wave costs the same for 1 or 148
+// ciphertexts, so splitting them only adds an exchange).
+static void level_slice(size_t B, int rank, int world, size_t shard_min, size_t *per, size_t *lo, size_t *hi) {
+    if (world <= 1 || B < shard_min * (size_t)world) { *per = 0; *lo = 0; *hi = B; return; }
+    *per = (B + world - 1) / world;
+    *lo = std::min(B, *per * (size_t)rank);
+    *hi = std::min(B, *per * (size_t)(rank + 1));
+}
+
+extern "C" int fhs_prog_plan(const fhs_prog *p, int rank, int world, size_t shard_min, uint64_t *levels_out,
+                             size_t cap_levels, size_t *n_levels) {
+    // levels_out[4*l + {0,1,2,3}] = B, blocks per rank (0 = replicated), lo, hi of this rank
+    if (!p || !n_levels || world < 1 || rank < 0 || rank >= world) return FHS_ERR_INVALID;
+    const Graph &g = p->g;
+    const int D = g.depth();
+    std::vector<size_t> cnt(D + 1, 0);
+    for (auto &n : g.nodes) if (n.kind == K_PBS) cnt[n.level]++;
+    size_t k = 0;
+    for (int l = 1; l <= D; l++) {
+        size_t per, lo, hi;
+        level_slice(cnt[l], rank, world, shard_min, &per, &lo, &hi);
+        if (levels_out && k < cap_levels) { levels_out[4 * k] = cnt[l]; levels_out[4 * k + 1] = per; levels_out[4 * k + 2] = lo; levels_out[4 * k + 3] = hi; }
+        k++;
+    }
+    *n_levels = k;
+    return FHS_OK;
+}
+
 extern "C" int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks,
                             uint64_t *out_blocks, double stats[4]) {
+    return fhs_prog_run_sharded(p, ctx, in_blocks, out_blocks, stats, 0, 1, 0, nullptr, nullptr);
+}
+
+extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks,
+                                    uint64_t *out_blocks, double stats[4], int rank, int world,
+                                    size_t shard_min, fhs_allgather_fn allgather, void *user) {
     if (!p || !ctx || (!in_blocks && p->n_inputs) || !out_blocks) return FHS_ERR_INVALID;
+    if (world < 1 || rank < 0 || rank >= world || (world > 1 && !allgather)) return FHS_ERR_INVALID;
+    if (shard_min == 0) shard_min = 148;
     const Graph &g = p->g;
     fhs_params prm;
     int rc = fhs_ctx_get_params(ctx, &prm);
@@ -220,7 +257,7 @@ extern "C" int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_
         if (g.nodes[i].kind == K_INPUT) slot[i] = (uint32_t)next++;
     if (next != p->n_inputs) return FHS_ERR_INVALID;
     fhs_pool *pool = nullptr;
-    if ((rc = fhs_pool_create(ctx, N ? N : 1, &pool)) != FHS_OK) return rc;
+    if ((rc = fhs_pool_create(ctx, (N ? N : 1) + (size_t)(D + 1) * world, &pool)) != FHS_OK) return rc;
     auto t_start = std::chrono::steady_clock::now();
     const uint64_t launches0 = fhs_launch_count(ctx);
     uint64_t n_pbs = 0, n_levels = 0;
@@ -246,9 +283,23 @@ extern "C" int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_
                 if (is_pbs) lut.push_back((uint32_t)n.lut);
                 slot[id] = (uint32_t)(next + (off.size() - 2));
             }
-            int r = fhs_level(pool, ids.size(), off.data(), idx.data(), coef.data(), cst.data(),
-                              is_pbs ? lut.data() : nullptr, tables.data(), g.luts.size(), next);
-            next += ids.size();
+            size_t per = 0, lo = 0, hi = ids.size();
+            if (is_pbs) level_slice(ids.size(), rank, world, shard_min, &per, &lo, &hi);
+            int r = FHS_OK;
+            if (hi > lo) {   // this rank's slice: descriptor rows [lo, hi)
+                std::vector<uint32_t> off2(hi - lo + 1);
+                for (size_t q = lo; q <= hi; q++) off2[q - lo] = off[q] - off[lo];
+                r = fhs_level(pool, hi - lo, off2.data(), idx.data() + off[lo], coef.data() + off[lo],
+                              cst.data() + lo, is_pbs ? lut.data() + lo : nullptr, tables.data(),
+                              g.luts.size(), next + lo);
+            }
+            if (r == FHS_OK && per) {  // exchange result blocks: rank q owns [next + q*per, next + (q+1)*per)
+                fhs_ctx_synchronize(ctx);
+                if (allgather(user, fhs_pool_device_ptr(pool) + next * width, per * width * sizeof(uint64_t)) != 0) r = FHS_ERR_COMM;
+                next += per * world;   // padded
+            } else {
+                next += ids.size();
+            }
             if (is_pbs) { n_pbs += ids.size(); n_levels++; }
             return r;
         };

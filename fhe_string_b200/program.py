@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "libfhs_string.so")
 _lib = None
 
-HOST_EXPORTS = ["fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
+HOST_EXPORTS = ["fhs_prog_run_sharded", "fhs_prog_plan", "fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
                 "fhs_prog_output_desc", "fhs_prog_export", "fhs_prog_run"]
 
 
@@ -33,6 +33,8 @@ def load_host_library():
     L.fhs_prog_output_desc.restype = ctypes.c_char_p
     L.fhs_prog_export.argtypes = [vp] * 11
     L.fhs_prog_run.argtypes = [vp, vp, vp, vp, vp]
+    L.fhs_prog_run_sharded.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, sz, vp, vp]
+    L.fhs_prog_plan.argtypes = [vp, ctypes.c_int, ctypes.c_int, sz, vp, sz, ctypes.POINTER(sz)]
     _lib = L
     return L
 
@@ -88,4 +90,46 @@ class Program:
         rc = self.L.fhs_prog_run(self.h, engine.h, inb.ctypes.data, out.ctypes.data, stats.ctypes.data)
         if rc != 0:
             raise FhsError(f"fhs_prog_run({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()}")
+        return out, dict(levels=int(stats[0]), pbs=int(stats[1]), launches=int(stats[2]), ms=float(stats[3]))
+
+    def plan(self, rank, world, shard_min=148):
+        """Per level: (B, blocks per rank or 0 if replicated, lo, hi) for `rank` of `world`."""
+        n = ctypes.c_size_t()
+        buf = np.zeros(4 * max(self.depth, 1), dtype=np.uint64)
+        rc = self.L.fhs_prog_plan(self.h, rank, world, shard_min, buf.ctypes.data, self.depth, ctypes.byref(n))
+        if rc != 0:
+            raise FhsError("fhs_prog_plan failed")
+        return buf[: 4 * n.value].reshape(-1, 4)
+
+    def run_sharded(self, engine, in_blocks, rank, world, shard_min=148):
+        """One process per GPU; every rank passes the same inputs.  Levels are split by rank and
+        re-assembled with torch.distributed.all_gather_into_tensor (NCCL over NVLink) in place on
+        the device pool."""
+        import torch
+        import torch.distributed as dist
+
+        class _Dev:  # raw device pointer -> torch tensor via __cuda_array_interface__
+            def __init__(self, ptr, n):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i8", "data": (ptr, False), "version": 3}
+
+        def _allgather(_user, base, bytes_per_rank):
+            try:
+                n = bytes_per_rank // 8
+                whole = torch.as_tensor(_Dev(base, n * world), device=torch.device("cuda", engine.device))
+                dist.all_gather_into_tensor(whole, whole[rank * n:(rank + 1) * n].clone())
+                torch.cuda.synchronize()
+                return 0
+            except Exception as e:  # never unwind into C
+                print("allgather failed:", e)
+                return 1
+
+        cb_t = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
+        cb = cb_t(_allgather)
+        inb = np.ascontiguousarray(in_blocks, dtype=np.uint64).reshape(self.n_inputs, -1)
+        out = np.empty((self.n_outputs, inb.shape[1] if self.n_inputs else engine.big), dtype=np.uint64)
+        stats = np.zeros(4, dtype=np.float64)
+        rc = self.L.fhs_prog_run_sharded(self.h, engine.h, inb.ctypes.data, out.ctypes.data, stats.ctypes.data,
+                                         rank, world, shard_min, ctypes.cast(cb, ctypes.c_void_p), None)
+        if rc != 0:
+            raise FhsError(f"fhs_prog_run_sharded({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()}")
         return out, dict(levels=int(stats[0]), pbs=int(stats[1]), launches=int(stats[2]), ms=float(stats[3]))

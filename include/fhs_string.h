@@ -58,6 +58,19 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
 int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks, uint64_t *out_blocks,
                  double stats[4]);
 
+/* Multi-GPU (one process per GPU, every rank holds a key replica and runs the same program on the
+ * same inputs): levels with at least shard_min * world evaluations (0 = default 148) are split
+ * contiguously by rank; after such a level `allgather(user, device_base, bytes_per_rank)` must make
+ * the world * bytes_per_rank bytes at device_base identical on all ranks (rank q contributes chunk q
+ * in place: ncclAllGather / torch.distributed.all_gather_into_tensor).  Smaller levels are
+ * replicated.  fhs_prog_plan reports, per level, {B, blocks per rank (0 = replicated), lo, hi}. */
+typedef int (*fhs_allgather_fn)(void *user, uint64_t *device_base, size_t bytes_per_rank);
+int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks, uint64_t *out_blocks,
+                         double stats[4], int rank, int world, size_t shard_min,
+                         fhs_allgather_fn allgather, void *user);
+int fhs_prog_plan(const fhs_prog *p, int rank, int world, size_t shard_min, uint64_t *levels_out,
+                  size_t cap_levels, size_t *n_levels);
+
 /* ---- client side (CPU): generate_keys / ClientKey of the reference ---------------------------
  * src/lib.rs:44-77 generate_keys_with_params(p, l); src/client_key.rs:16-62; mod.rs:58-92,121-129.
  * Not accelerated (one-off CPU work in the reference too).  seed == 0 draws from the OS. */
