@@ -194,6 +194,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-op-latency", action="store_true", help="skip the string-op latency block (ncu runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -375,7 +376,7 @@ def main():
                     "ms_per_step": e2e_ms / args.steps},
             "clocks": clocks,
         }
-        if world == 1:
+        if world == 1 and not args.no_op_latency:
             line["op_latency"] = string_op_latency(ck, eng)
         if world == 1 and not args.no_cpu_baseline:
             from oracle import oracle as O      # the cpu_baseline leg: the only use of oracle/ here

@@ -129,7 +129,9 @@ constexpr int kSlots2 = 4;
 constexpr int kComputeThreads2 = 64 * kSlots2;   // 256
 constexpr int kLoaderThreads2 = 128;             // one loader warp per TMEM lane quarter
 constexpr int kThreads2 = kComputeThreads2 + kLoaderThreads2;
-constexpr int kBarFull = 5, kBarFree = 6;
+constexpr int kBarFull = 5, kBarFree = 6;     // group 0 (or the whole CTA when not staggered)
+constexpr int kBarFull1 = 7, kBarFree1 = 8;   // group 1 (slots 2, 3) in staggered mode
+constexpr int kBarTokA = 9, kBarTokB = 10;    // transpose token: A = group 0 -> 1, B = group 1 -> 0
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemBskCol = 256;
 
@@ -167,11 +169,17 @@ __device__ __forceinline__ void ldg_b128(const void *p, uint32_t &a, uint32_t &b
                  : "l"(p));
 }
 
+// kOpt bit 0: inverse twiddles (the row T[rk2][0..31] every thread multiplies by after the inverse
+// row pass) live in the 128 TMEM columns the accumulator and the BSK slice leave free, instead of
+// being re-read from shared memory every iteration (shared-memory wavefronts are as scarce as FP64
+// issue slots in this kernel: ncu shows elapsed = FP64 cycles + LSU wavefronts).
+template <int kOpt, int kStag>
 __global__ void __launch_bounds__(kThreads2, 1)
 blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__restrict__ lut_id,
                        const uint64_t *__restrict__ lut_tables, const double2 *__restrict__ bsk_f,
                        const double2 *__restrict__ twiddle_g, uint64_t *__restrict__ lwe_out,
-                       unsigned int batch, int n_lwe, int log_box, uint64_t delta, int active_slots) {
+                       unsigned int batch, int n_lwe, int log_box, uint64_t delta, int active_slots,
+                       int stagger_rt) {
     // active_slots in {1, 2, 4}: small levels use fewer ciphertexts per CTA (more CTAs, shorter
     // iterations); idle compute / loader warps skip the main loops entirely.
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -187,7 +195,14 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
     const uint32_t tbase = sm.tmem_base + (((uint32_t)(warp & 3) * 32u) << 16);
     const unsigned int n_groups = (batch + active_slots - 1) / active_slots;
     const int active_loaders = active_slots == 1 ? 2 : 4;
-    const int bar_threads = 64 * active_slots + 32 * active_loaders;
+    // Staggered mode (4 slots): slots {0,1} and {2,3} form two groups with their own full / free
+    // barriers.  Every SM sub-partition hosts one warp of each group; a token passed between the
+    // groups serialises their shared-memory transposes (G0, G1, G0, G1, ...), which keeps the groups
+    // out of phase: while one group is in an LSU-only transpose the other owns the FP64 pipe.
+    // kStag 0/1/2: compile-time (launched with active_slots == kSlots2 only); 3: run-time flag
+    const bool stag = kStag == 3 ? (stagger_rt && active_slots == kSlots2) : (kStag != 0);
+    constexpr bool tok_early = kStag == 2; // hand the transpose token over right after the slot barrier
+    const int bar_threads = stag ? 128 + 32 * active_loaders : 64 * active_slots + 32 * active_loaders;
 
     if (warp >= 2 * kSlots2) {
         const bool loader_active = (warp & 3) < active_loaders;
@@ -212,6 +227,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                     }
                     if (b == 0 && !first) {     // previous slice fully consumed?
                         named_bar_sync(kBarFree, bar_threads);
+                        if (stag) named_bar_sync(kBarFree1, bar_threads);
                         tmem_fence_after_sync();
                     }
                     tmem_st32(tbase + kTmemBskCol + 32 * b, r);
@@ -220,6 +236,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 tmem_wait_st();
                 tmem_fence_before_sync();
                 named_bar_arrive(kBarFull, bar_threads);
+                if (stag) named_bar_arrive(kBarFull1, bar_threads);
             }
         }
     } else {
@@ -234,7 +251,32 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
         uint32_t *__restrict__ H = ss.hi[w];
         const uint32_t tacc = tbase + (uint32_t)(warp >> 2) * 128u;  // 64 columns: high words of 64 coefficients
         const uint32_t tbsk = tbase + kTmemBskCol;
+        // free TMEM columns of this lane quarter: [64,128) and [192,256); warps q and q+4 share the
+        // quarter and have the same (w, lane) -> the same twiddle row, so both write identical data.
+        const uint32_t ttw0 = tbase + 64, ttw1 = tbase + 192;
+        if ((kOpt & 1) && slot < active_slots) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                uint32_t tw[64];
+#pragma unroll
+                for (int q = 0; q < 16; q++) {
+                    const double2 t = sm.T[rk2 * kTStride + 16 * h + q];
+                    tw[4 * q + 0] = (uint32_t)__double2loint(t.x);
+                    tw[4 * q + 1] = (uint32_t)__double2hiint(t.x);
+                    tw[4 * q + 2] = (uint32_t)__double2loint(t.y);
+                    tw[4 * q + 3] = (uint32_t)__double2hiint(t.y);
+                }
+                tmem_st64(h ? ttw1 : ttw0, tw);
+            }
+            tmem_wait_st();
+        }
         const unsigned int last_group = ((n_groups - 1 - blockIdx.x) / gridDim.x) * gridDim.x + blockIdx.x;
+        const int grp = stag ? (warp >> 2) : 0;
+        const int bar_full = grp ? kBarFull1 : kBarFull;
+        const int bar_free = grp ? kBarFree1 : kBarFree;
+        const int tok_wait = grp ? kBarTokA : kBarTokB;   // token this group waits for
+        const int tok_pass = grp ? kBarTokB : kBarTokA;   // token this group hands over
+        if (stag && grp == 1) named_bar_arrive(kBarTokB, 256);  // group 0 owns the first transpose
 
         for (unsigned int g = blockIdx.x; slot < active_slots && g < n_groups; g += gridDim.x) {
             unsigned int ct = g * active_slots + slot;
@@ -288,6 +330,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                     }
                 }
                 fwd_cols(xr, xi, sm.T, lane);
+                if (stag) named_bar_sync(tok_wait, 256);
                 {
                     double2 *__restrict__ Sw = ss.S[w];
 #pragma unroll
@@ -295,6 +338,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         Sw[k2 * kTStride + lane] = make_double2(xr[k2], xi[k2]);
                 }
                 slot_bar(slot);
+                if (stag && tok_early) named_bar_arrive(tok_pass, 256);
                 {
                     const double2 *__restrict__ Sr = ss.S[rp] + rk2 * kTStride;
 #pragma unroll
@@ -304,9 +348,10 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         xi[FHS_BR5(n1)] = v.y;
                     }
                 }
+                if (stag && !tok_early) named_bar_arrive(tok_pass, 256);
                 fft32_pos(xr, xi);
                 // ---- GGSW contraction against the BSK slice parked in TMEM ----
-                named_bar_sync(kBarFull, bar_threads);
+                named_bar_sync(bar_full, bar_threads);
                 tmem_fence_after_sync();
 #pragma unroll
                 for (int b = 0; b < 8; b++) {
@@ -331,7 +376,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 }
                 if (!(g == last_group && i == n_lwe - 1)) {
                     tmem_fence_before_sync();
-                    named_bar_arrive(kBarFree, bar_threads);
+                    named_bar_arrive(bar_free, bar_threads);
                 }
 #pragma unroll
                 for (int q = 0; q < 32; q++) {
@@ -342,7 +387,23 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 }
                 // ---- inverse row pass, conjugate twiddle, transpose back ----
                 fft32_neg(xr, xi);
-                {
+                if (kOpt & 1) {
+#pragma unroll
+                    for (int c = 0; c < 8; c++) {   // 4 twiddles (16 columns) per TMEM load
+                        uint32_t tw[16];
+                        tmem_ld16(((c & 4) ? ttw1 : ttw0) + 16 * (c & 3), tw);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            const int n1 = 4 * c + k;
+                            const double tx = __hiloint2double((int)tw[4 * k + 1], (int)tw[4 * k + 0]);
+                            const double ty = __hiloint2double((int)tw[4 * k + 3], (int)tw[4 * k + 2]);
+                            const double a0 = xr[n1], b0 = xi[n1];
+                            xr[n1] = a0 * tx + b0 * ty;
+                            xi[n1] = b0 * tx - a0 * ty;
+                        }
+                    }
+                } else {
                     const double2 *__restrict__ Tr = sm.T + rk2 * kTStride;
 #pragma unroll
                     for (int n1 = 0; n1 < 32; n1++) {
@@ -352,12 +413,16 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         xi[n1] = b0 * t.x - a0 * t.y;
                     }
                 }
+                if (stag) named_bar_sync(tok_wait, 256);
                 {
                     double2 *__restrict__ Sq = ss.S[rp] + rk2 * kTStride;
 #pragma unroll
                     for (int n1 = 0; n1 < 32; n1++) Sq[n1] = make_double2(xr[n1], xi[n1]);
                 }
                 slot_bar(slot);
+                // the last token of the kernel is not handed over (nobody would collect it)
+                const bool pass_tok = stag && !(grp == 1 && g == last_group && i == n_lwe - 1);
+                if (pass_tok && tok_early) named_bar_arrive(tok_pass, 256);
                 {
                     const double2 *__restrict__ Sw = ss.S[w];
 #pragma unroll
@@ -367,6 +432,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         xi[FHS_BR5(k2)] = v.y;
                     }
                 }
+                if (pass_tok && !tok_early) named_bar_arrive(tok_pass, 256);
                 fft32_neg(xr, xi);
                 // ---- conjugate pre-twist, add as torus into the TMEM accumulator ----
 #pragma unroll
@@ -520,10 +586,13 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
                         const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
     static bool attr_set = false;
+    static int stagger = 4, opt = 1;   // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1)
     if (!attr_set) {
-        FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(Smem2)));
+        if (const char *e = getenv("FHS_BR_STAGGER")) stagger = atoi(e);
+        if (const char *e = getenv("FHS_BR_OPT")) opt = atoi(e) & 1;
+#define FHS_BR_ATTR(o, st) FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel<o, st>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem2)))
+        FHS_BR_ATTR(0, 0); FHS_BR_ATTR(0, 3); FHS_BR_ATTR(1, 0); FHS_BR_ATTR(1, 3);
+#undef FHS_BR_ATTR
         attr_set = true;
     }
     const int log_box = ilog2(kN / c->space);
@@ -532,9 +601,19 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
         const int active = batch <= (size_t)c->sm_count ? 1 : (batch <= 2 * (size_t)c->sm_count ? 2 : kSlots2);
         size_t ctas = (batch + active - 1) / active;
         if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
-        blind_rotate_v2_kernel<<<(unsigned)ctas, kThreads2, sizeof(Smem2), c->stream>>>(
+        // stagger: 0 = plain kernel, 3/4 = kernel with the run-time stagger flag off/on (default 4).
+        // The flagged kernel is the fast one even with the flag off: ptxas keeps the predicated
+        // token barriers next to the transposes, which it does not for the compile-time variants.
+        const int st = stagger;
+        using kern_t = void (*)(const uint64_t *, const uint32_t *, const uint64_t *, const double2 *,
+                                const double2 *, uint64_t *, unsigned int, int, int, uint64_t, int, int);
+        static const kern_t table[2][2] = {{blind_rotate_v2_kernel<0, 0>, blind_rotate_v2_kernel<0, 3>},
+                                           {blind_rotate_v2_kernel<1, 0>, blind_rotate_v2_kernel<1, 3>}};
+        kern_t kern = table[opt][st >= 3 ? 1 : 0];
+        const int stagger_rt = st == 4;
+        kern<<<(unsigned)ctas, kThreads2, sizeof(Smem2), c->stream>>>(
             d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, (unsigned int)batch,
-            (int)c->n, log_box, delta, active);
+            (int)c->n, log_box, delta, active, stagger_rt);
     }
     c->launches++;
     FHS_CUDA(cudaGetLastError());
