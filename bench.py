@@ -345,6 +345,12 @@ def main():
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+        traffic = {}
+        try:    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            traffic = {k: v["dram_bytes_read"] + v["dram_bytes_write"] for k, v in tj.items() if isinstance(v, dict)}
+        except Exception:
+            pass
         achieved_tf = batch * FLOP_PER_PBS / (br_ms * 1e-3) / 1e12
         ks_bytes = 60_866_560 + batch * (16_392 + 5_944)
         ks_gbs = ks_bytes / (ks_ms * 1e-3) / 1e9 if ks_ms > 0 else None
@@ -361,13 +367,14 @@ def main():
             "kernels_per_step": {"keyswitch_ms": ks_ms, "blind_rotate_ms": br_ms},
             "roofline": {"bound": "fp64", "kernel": "blind_rotate_kernel", "achieved": achieved_tf,
                          "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved_tf / fp64_peak,
-                         "traffic": None,
+                         "traffic": traffic.get("blind_rotate") if batch == BATCH else None,
                          "peak_source": "measured in this run: DFMA chains (fhs_measure_fp64_tflops); "
                                         "MEASURED_PEAKS.json has no FP64 figure",
                          "algorithmic": f"{FLOP_PER_PBS} flop/PBS x {batch} PBS per launch"},
             "roofline_keyswitch": {"bound": "hbm", "kernel": "keyswitch_kernel", "achieved": ks_gbs,
                                    "peak": hbm_peak, "unit": "GB/s",
                                    "frac": (ks_gbs / hbm_peak) if ks_gbs else None,
+                                   "traffic": traffic.get("keyswitch") if batch == BATCH else None,
                                    "peak_source": hbm_src,
                                    "algorithmic": f"{ks_bytes} B per launch (KSK once + B x (16392 + 5944))"},
             "e2e": {"value": e2e_val, "unit": "PBS/s",

@@ -199,9 +199,11 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
     // barriers.  Every SM sub-partition hosts one warp of each group; a token passed between the
     // groups serialises their shared-memory transposes (G0, G1, G0, G1, ...), which keeps the groups
     // out of phase: while one group is in an LSU-only transpose the other owns the FP64 pipe.
-    // kStag 0/1/2: compile-time (launched with active_slots == kSlots2 only); 3: run-time flag
-    const bool stag = kStag == 3 ? (stagger_rt && active_slots == kSlots2) : (kStag != 0);
-    constexpr bool tok_early = kStag == 2; // hand the transpose token over right after the slot barrier
+    // kStag 0: no stagger code (baseline for A/B runs); 3: stagger behind a run-time flag.  The flag
+    // is deliberately NOT a template parameter: with predicated token barriers ptxas keeps the
+    // hand-over next to the transposed reads; the compile-time variant sank it below the FFT and
+    // was 6 ms slower.
+    const bool stag = kStag != 0 && stagger_rt && active_slots == kSlots2;
     const int bar_threads = stag ? 128 + 32 * active_loaders : 64 * active_slots + 32 * active_loaders;
 
     if (warp >= 2 * kSlots2) {
@@ -338,7 +340,6 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         Sw[k2 * kTStride + lane] = make_double2(xr[k2], xi[k2]);
                 }
                 slot_bar(slot);
-                if (stag && tok_early) named_bar_arrive(tok_pass, 256);
                 {
                     const double2 *__restrict__ Sr = ss.S[rp] + rk2 * kTStride;
 #pragma unroll
@@ -348,7 +349,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         xi[FHS_BR5(n1)] = v.y;
                     }
                 }
-                if (stag && !tok_early) named_bar_arrive(tok_pass, 256);
+                if (stag) named_bar_arrive(tok_pass, 256);
                 fft32_pos(xr, xi);
                 // ---- GGSW contraction against the BSK slice parked in TMEM ----
                 named_bar_sync(bar_full, bar_threads);
@@ -422,7 +423,6 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 slot_bar(slot);
                 // the last token of the kernel is not handed over (nobody would collect it)
                 const bool pass_tok = stag && !(grp == 1 && g == last_group && i == n_lwe - 1);
-                if (pass_tok && tok_early) named_bar_arrive(tok_pass, 256);
                 {
                     const double2 *__restrict__ Sw = ss.S[w];
 #pragma unroll
@@ -432,7 +432,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         xi[FHS_BR5(k2)] = v.y;
                     }
                 }
-                if (pass_tok && !tok_early) named_bar_arrive(tok_pass, 256);
+                if (pass_tok) named_bar_arrive(tok_pass, 256);
                 fft32_neg(xr, xi);
                 // ---- conjugate pre-twist, add as torus into the TMEM accumulator ----
 #pragma unroll
@@ -591,7 +591,7 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
         if (const char *e = getenv("FHS_BR_STAGGER")) stagger = atoi(e);
         if (const char *e = getenv("FHS_BR_OPT")) opt = atoi(e) & 1;
 #define FHS_BR_ATTR(o, st) FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel<o, st>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem2)))
-        FHS_BR_ATTR(0, 0); FHS_BR_ATTR(0, 3); FHS_BR_ATTR(1, 0); FHS_BR_ATTR(1, 3);
+        FHS_BR_ATTR(0, 0); FHS_BR_ATTR(1, 3);
 #undef FHS_BR_ATTR
         attr_set = true;
     }
@@ -607,9 +607,9 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
         const int st = stagger;
         using kern_t = void (*)(const uint64_t *, const uint32_t *, const uint64_t *, const double2 *,
                                 const double2 *, uint64_t *, unsigned int, int, int, uint64_t, int, int);
-        static const kern_t table[2][2] = {{blind_rotate_v2_kernel<0, 0>, blind_rotate_v2_kernel<0, 3>},
-                                           {blind_rotate_v2_kernel<1, 0>, blind_rotate_v2_kernel<1, 3>}};
-        kern_t kern = table[opt][st >= 3 ? 1 : 0];
+        // FHS_BR_OPT=0 FHS_BR_STAGGER=0 selects the round-1 baseline kernel (A/B runs); default is
+        // the TMEM-twiddle kernel with the stagger flag on (4); 3 = same kernel, flag off.
+        kern_t kern = (opt == 0 && st == 0) ? blind_rotate_v2_kernel<0, 0> : blind_rotate_v2_kernel<1, 3>;
         const int stagger_rt = st == 4;
         kern<<<(unsigned)ctas, kThreads2, sizeof(Smem2), c->stream>>>(
             d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, (unsigned int)batch,
