@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "libfhs_string.so")
 _lib = None
 
-HOST_EXPORTS = ["fhs_prog_run_sharded", "fhs_prog_plan", "fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
+HOST_EXPORTS = ["fhs_prog_run_many", "fhs_prog_run_sharded", "fhs_prog_plan", "fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
                 "fhs_prog_output_desc", "fhs_prog_export", "fhs_prog_run"]
 
 
@@ -33,6 +33,7 @@ def load_host_library():
     L.fhs_prog_output_desc.restype = ctypes.c_char_p
     L.fhs_prog_export.argtypes = [vp] * 11
     L.fhs_prog_run.argtypes = [vp, vp, vp, vp, vp]
+    L.fhs_prog_run_many.argtypes = [vp, vp, sz, vp, vp, vp]
     L.fhs_prog_run_sharded.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, sz, vp, vp]
     L.fhs_prog_plan.argtypes = [vp, ctypes.c_int, ctypes.c_int, sz, vp, sz, ctypes.POINTER(sz)]
     _lib = L
@@ -90,6 +91,19 @@ class Program:
         rc = self.L.fhs_prog_run(self.h, engine.h, inb.ctypes.data, out.ctypes.data, stats.ctypes.data)
         if rc != 0:
             raise FhsError(f"fhs_prog_run({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()}")
+        return out, dict(levels=int(stats[0]), pbs=int(stats[1]), launches=int(stats[2]), ms=float(stats[3]))
+
+    def run_many(self, engine, in_blocks):
+        """M independent instances: in_blocks u64 [M][n_inputs][2049] -> ([M][n_outputs][2049], stats).
+        Every level runs for all instances at once (fhs_prog_run_many)."""
+        inb = np.ascontiguousarray(in_blocks, dtype=np.uint64)
+        m = inb.shape[0]
+        inb = inb.reshape(m, self.n_inputs, -1)
+        out = np.empty((m, self.n_outputs, inb.shape[2]), dtype=np.uint64)
+        stats = np.zeros(4, dtype=np.float64)
+        rc = self.L.fhs_prog_run_many(self.h, engine.h, m, inb.ctypes.data, out.ctypes.data, stats.ctypes.data)
+        if rc != 0:
+            raise FhsError(f"fhs_prog_run_many({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()}")
         return out, dict(levels=int(stats[0]), pbs=int(stats[1]), launches=int(stats[2]), ms=float(stats[3]))
 
     def plan(self, rank, world, shard_min=148):

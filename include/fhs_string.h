@@ -58,6 +58,14 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
 int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks, uint64_t *out_blocks,
                  double stats[4]);
 
+/* M independent instances of the same program in one pass (e.g. the 1024 string comparisons of a
+ * throughput sweep): in_blocks [M][n_inputs][k*N+1], out_blocks [M][n_outputs][k*N+1].  Every level
+ * is evaluated for all instances at once (chunks of <= 32768 LUT evaluations per fhs_level call), so
+ * levels that are small per instance still fill the GPU.  Independent instances need no exchange:
+ * multi-GPU callers give each rank its own slice of the instances. */
+int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_instances, const uint64_t *in_blocks,
+                      uint64_t *out_blocks, double stats[4]);
+
 /* Multi-GPU (one process per GPU, every rank holds a key replica and runs the same program on the
  * same inputs): levels with at least shard_min * world evaluations (0 = default 148) are split
  * contiguously by rank; after such a level `allgather(user, device_base, bytes_per_rank)` must make

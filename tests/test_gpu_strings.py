@@ -86,3 +86,24 @@ def test_split_and_replace_cmd_config(engine, keyset):
         vals = [b for c in p_chars for b in to_blocks(c)] + [b for u in usz for b in usize_blocks(u)]
         out, _ = p.run(engine, keyset.encrypt(np.array(vals, dtype=np.uint64), seed=5))
         assert decode(p.desc, [int(x) for x in keyset.decrypt(out)]) == w
+
+
+def test_run_many_independent_comparisons(engine, keyset):
+    """BASELINE configs[4] in miniature: M independent (a, b) pairs through fhs_prog_run_many (every
+    level evaluated for all instances at once) give the same booleans as Python's str compare."""
+    rng = np.random.default_rng(13)
+    pairs = []
+    for i in range(12):
+        a = "".join(chr(int(c)) for c in rng.integers(97, 123, 6))
+        b = a if i % 3 == 0 else a[:3] + "".join(chr(int(c)) for c in rng.integers(97, 123, 3))
+        pairs.append((a, b))
+    for op, f in (("eq", lambda a, b: a == b), ("lt", lambda a, b: a < b), ("contains", lambda a, b: b[:3] in a)):
+        rhs = [(a, b[:3]) if op == "contains" else (a, b) for a, b in pairs]
+        chars = [[enc_chars(a, 8), enc_chars(b, 8 if op != "contains" else None)] for a, b in rhs]
+        p = Program(op, [len(c) for c in chars[0]], 0, (), 4, 4)
+        vals = np.array([[v for c in inst for v in to_blocks(c)] for inst in chars], dtype=np.uint64)
+        cts = keyset.encrypt(vals.reshape(-1), seed=23).reshape(len(pairs), p.n_inputs, -1)
+        out, st = p.run_many(engine, cts)
+        assert st["pbs"] == p.pbs_count * len(pairs) and st["levels"] == p.depth
+        got = [decode(p.desc, [int(x) for x in keyset.decrypt(out[m])], 4) for m in range(len(pairs))]
+        assert got == [f(a, b) for a, b in pairs]
