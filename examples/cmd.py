@@ -76,6 +76,8 @@ def main():
         ("ends_with", lambda: s.endswith(p), lambda: es.ends_with(sk, ep)),
         ("to_lowercase", lambda: s.lower(), lambda: es.to_lowercase(sk)),
         ("to_uppercase", lambda: s.upper(), lambda: es.to_uppercase(sk)),
+        ("add", lambda: (s + p)[:L], lambda: es.add(sk, ep)),
+        ("repeat", lambda: (s * n)[:L], lambda: es.repeat(sk, en, min(L, len(s * n)))),
         ("trim", lambda: s.strip(WS), lambda: es.trim(sk)),
         ("trim_start", lambda: s.lstrip(WS), lambda: es.trim_start(sk)),
         ("trim_end", lambda: s.rstrip(WS), lambda: es.trim_end(sk)),

@@ -265,5 +265,9 @@ FheString.substr_to = lambda self, k, index: k.run("substr_to", [self], [index])
 FheString.substr_from = lambda self, k, index: k.run("substr_from", [self], [index])
 FheString.splitn = lambda self, k, n, p: k.run("splitn", [self, p], [n])
 FheString.rsplitn = lambda self, k, n, p: k.run("rsplitn", [self, p], [n])
+# insert.rs:14-124
+FheString.add = lambda self, k, s: k.run("add", [self, s])
+FheString.insert = lambda self, k, index, s: k.run("insert", [self, s], [index])
+FheString.repeat = lambda self, k, n, l: k.run("repeat", [self], [n], (int(l),))
 FheString.replace = lambda self, k, p, s, l: k.run("replace", [self, p, s], (), (int(l),))
 FheString.replacen = lambda self, k, p, s, n, l: k.run("replacen", [self, p, s], [n], (int(l),))

@@ -5,7 +5,7 @@
 #include <vector>
 
 #include "../../../include/fhs_string.h"
-#include "replace.hpp"
+#include "insert.hpp"
 
 using namespace fhs_host;
 
@@ -22,7 +22,7 @@ thread_local std::string g_host_err;
 
 struct Builder {
     fhs_prog &P;
-    ReplaceOps ops;
+    InsertOps ops;
     Builder(fhs_prog &p, size_t nbc, size_t nbu) : P(p), ops(p.g, nbc, nbu) {}
 
     FStr in_str(size_t n_chars) {
@@ -49,7 +49,7 @@ struct Builder {
 
 int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t n_strings,
              size_t n_usize_args, const uint64_t *scalars, size_t n_scalars) {
-    ReplaceOps &o = B.ops;
+    InsertOps &o = B.ops;
     std::vector<FStr> S;
     for (size_t i = 0; i < n_strings; i++) {
         if (n_chars[i] == 0) { g_host_err = "a string has at least its terminator"; return FHS_ERR_INVALID; }
@@ -125,6 +125,21 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
         uint64_t maxlen = (o.nb_usize >= 16) ? ~0ull : ((1ull << (2 * o.nb_usize)) - 1);
         size_t l = (size_t)std::min<uint64_t>(scalars[0], maxlen);
         FStr r = op == "replace" ? o.replace(S[0], S[1], S[2], l) : o.replacen(S[0], S[1], S[2], U[0], l);
+        B.out_str(r); B.P.desc = str_desc(r);
+    }
+    else if (op == "add") {           // insert.rs:14  operands: a, b
+        if (!need(2, 0)) return bad();
+        FStr r = o.add_str(S[0], S[1]);
+        B.out_str(r); B.P.desc = str_desc(r);
+    }
+    else if (op == "insert") {        // insert.rs:48  operands: a, s; usize index
+        if (!need(2, 1)) return bad();
+        FStr r = o.insert(S[0], U[0], S[1]);
+        B.out_str(r); B.P.desc = str_desc(r);
+    }
+    else if (op == "repeat") {        // insert.rs:20  operands: a; usize n; scalars[0] = l
+        if (!need(1, 1) || n_scalars < 1) return bad();
+        FStr r = o.repeat(S[0], U[0], (size_t)scalars[0]);
         B.out_str(r); B.P.desc = str_desc(r);
     }
     else { g_host_err = "unknown op " + op; return FHS_ERR_INVALID; }

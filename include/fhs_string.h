@@ -3,7 +3,7 @@
  * programs and executed on the GPU through include/fhs_cuda.h.
  *
  * Replaces the bodies of the reference's FheString methods (src/ciphertext/compare.rs:15-151,
- * convert.rs:14-61, search.rs:17-244, trim.rs:15-132, split.rs:238-515, replace.rs:17-104, mod.rs:132-237):
+ * convert.rs:14-61, search.rs:17-244, trim.rs:15-132, split.rs:238-515, replace.rs:17-104, insert.rs:14-124, mod.rs:132-237):
  * instead of issuing one tfhe-rs PBS at a time under rayon, an operation is built ONCE per operand
  * shape as a DAG of LUT evaluations over linear combinations of blocks; all nodes of equal depth
  * form one level = one fhs_level call.  Ciphertexts are plain tfhe shortint LWE containers
@@ -27,7 +27,8 @@ typedef struct fhs_prog fhs_prog;
 /* Build the program of operation `op` (the reference method name: "eq", "ne", "lt", "le", "gt",
  * "ge", "eq_ignore_ascii_case", "is_empty", "len", "to_uppercase", "to_lowercase", "contains",
  * "find", "rfind", "starts_with", "ends_with", "trim", "trim_start", "trim_end", "strip_prefix",
- * "strip_suffix", "substr_to", "substr_from", ...) for operand shapes:
+ * "strip_suffix", "substr_to", "substr_from", "split*", "replace", "replacen", "add", "insert",
+ * "repeat", ...) for operand shapes:
  *   n_chars[i] = number of FheAsciiChar of string operand i (terminator and padding included),
  *   n_usize_args = number of FheUsize operands that follow the strings,
  *   scalars = clear arguments of the method (e.g. l of replace, clear n), may be NULL.

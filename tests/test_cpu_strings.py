@@ -173,3 +173,19 @@ def test_replace(a, p, s, pa, pp, ps):
     for n in (0, 1, 2, 5):
         wn = a.replace(p, s, n)
         assert run("replacen", [a, p, s], [pa, pp, ps], usizes=[n], scalars=[len(wn) + 1]) == wn
+
+
+# insert.rs:14-124 (tables in the style of tests/insert.rs:20-45,76-95)
+@pytest.mark.parametrize("a,b,pa,pb", [("abc", "xy", None, None), ("", "", None, None), ("a", "", None, None),
+                                       ("", "b", None, None), ("abc", "xy", 5, 4), ("hello", "world", 7, None)])
+def test_add_and_insert(a, b, pa, pb):
+    assert run("add", [a, b], [pa, pb]) == a + b
+    for i in range(len(a) + 1):
+        assert run("insert", [a, b], [pa, pb], usizes=[i]) == a[:i] + b + a[i:]
+
+
+@pytest.mark.parametrize("a,pa", [("ab", None), ("abc", 4), ("", None), ("x", None), ("", 3)])
+def test_repeat(a, pa):
+    for n in (0, 1, 2, 3, 5, 8, 20):
+        for l in (0, 1, 4, 7, 16):
+            assert run("repeat", [a], [pa], usizes=[n], scalars=(l,)) == (a * n)[:l]

@@ -107,3 +107,15 @@ def test_run_many_independent_comparisons(engine, keyset):
         assert st["pbs"] == p.pbs_count * len(pairs) and st["levels"] == p.depth
         got = [decode(p.desc, [int(x) for x in keyset.decrypt(out[m])], 4) for m in range(len(pairs))]
         assert got == [f(a, b) for a, b in pairs]
+
+
+def test_add_insert_repeat(engine, keyset):
+    """insert.rs:14-124 on the GPU: add / insert / repeat of the cmd config strings."""
+    s, pat = " A bcbc ", "bc"
+    assert run_gpu(engine, keyset, "add", [s, pat])[0] == s + pat
+    assert run_gpu(engine, keyset, "insert", [s, pat], usizes=[3])[0] == s[:3] + pat + s[3:]
+    chars = [enc_chars(pat)]
+    p = Program("repeat", [len(chars[0])], 1, (6,), 4, 4)
+    vals = to_blocks(chars[0]) + usize_blocks(3)
+    out, _ = p.run(engine, keyset.encrypt(np.array(vals, dtype=np.uint64), seed=9))
+    assert decode(p.desc, [int(x) for x in keyset.decrypt(out)]) == pat * 3
