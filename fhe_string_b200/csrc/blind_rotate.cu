@@ -136,17 +136,21 @@ constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemBskCol = 256;
 
 struct SlotSmem2 {
-    uint32_t hi[2][kN];      // high words of the accumulator polynomials
     double2 S[2][kTile];     // transpose tiles
     uint16_t amod[768];
 };
 struct Smem2 {
+    // high words of the accumulator polynomials, first so that every 8 KB plane is 8 KB aligned in
+    // the shared window (the kernel aligns the struct itself): a rotated read address is then
+    // plane | (offset & 0x1FFC) -- one LOP3 -- and its partner (+N/2) is address ^ 0x1000.
+    uint32_t hi[kSlots2][2][kN];
     double2 T[kTile];
     SlotSmem2 slot[kSlots2];
     uint32_t tmem_base;
     uint32_t pad[3];
 };
-static_assert(sizeof(Smem2) <= 227 * 1024, "shared memory budget (v2)");
+constexpr size_t kSmem2Bytes = sizeof(Smem2) + 8192 - 16;   // worst-case alignment padding
+static_assert(kSmem2Bytes <= 227 * 1024, "shared memory budget (v2)");
 
 __device__ __forceinline__ void named_bar_sync(int id, int n) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
@@ -169,6 +173,8 @@ __device__ __forceinline__ void ldg_b128(const void *p, uint32_t &a, uint32_t &b
                  : "l"(p));
 }
 
+// kOpt bit 2: rotated gather of the hi plane with one LOP3 per address (8 KB aligned planes) and the
+// negacyclic sign taken from a pre-shifted offset (-160 integer instructions per CMUX).
 // kOpt bit 0: inverse twiddles (the row T[rk2][0..31] every thread multiplies by after the inverse
 // row pass) live in the 128 TMEM columns the accumulator and the BSK slice leave free, instead of
 // being re-read from shared memory every iteration (shared-memory wavefronts are as scarce as FP64
@@ -183,7 +189,8 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
     // active_slots in {1, 2, 4}: small levels use fewer ciphertexts per CTA (more CTAs, shorter
     // iterations); idle compute / loader warps skip the main loops entirely.
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    Smem2 &sm = *reinterpret_cast<Smem2 *>(smem_raw);
+    const uint32_t smem_pad = (0u - (uint32_t)__cvta_generic_to_shared(smem_raw)) & 8191u;
+    Smem2 &sm = *reinterpret_cast<Smem2 *>(smem_raw + smem_pad);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
@@ -250,7 +257,8 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
         const int table_len = kN >> log_box;
         const int rp = lane >> 4;
         const int rk2 = 16 * w + (lane & 15);
-        uint32_t *__restrict__ H = ss.hi[w];
+        uint32_t *__restrict__ H = sm.hi[slot][w];
+        const uint32_t h_plane = (uint32_t)__cvta_generic_to_shared(H);   // 8 KB aligned
         const uint32_t tacc = tbase + (uint32_t)(warp >> 2) * 128u;  // 64 columns: high words of 64 coefficients
         const uint32_t tbsk = tbase + kTmemBskCol;
         // free TMEM columns of this lane quarter: [64,128) and [192,256); warps q and q+4 share the
@@ -310,16 +318,31 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                     uint32_t own[64];
                     tmem_ld64(tacc, own);
                     const uint32_t base = (uint32_t)(lane - (int)a) & (2 * kN - 1);
+                    // byte offset of coefficient (lane - a) mod 2N, pre-shifted so that the
+                    // negacyclic sign (bit 13) is the top bit: + (m << 25) walks the 32 rows mod 2^32
+                    const uint32_t off_s = base << 20;
                     tmem_wait_ld();
 #pragma unroll
                     for (int m = 0; m < 32; m++) {
-                        const uint32_t idx0 = (base + 32 * m) & (2 * kN - 1);
-                        const uint32_t idx1 = (idx0 + kH) & (2 * kN - 1);
-                        uint32_t r0 = H[idx0 & (kN - 1)];
-                        uint32_t r1 = H[idx1 & (kN - 1)];
-                        // negacyclic wrap: -x on the high word is ~x up to the dropped borrow
-                        r0 ^= (uint32_t)((int)(idx0 << 20) >> 31);
-                        r1 ^= (uint32_t)((int)(idx1 << 20) >> 31);
+                        uint32_t r0, r1;
+                        if (kOpt & 4) {
+                            const uint32_t t0 = off_s + ((uint32_t)m << 25);     // idx0 << 20
+                            const uint32_t t1 = t0 + (1u << 30);                // (idx0 + N/2) << 20
+                            const uint32_t a0 = h_plane | ((t0 >> 18) & 0x1FFCu);
+                            const uint32_t a1 = a0 ^ 0x1000u;
+                            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r0) : "r"(a0) : "memory");
+                            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r1) : "r"(a1) : "memory");
+                            r0 ^= (uint32_t)((int)t0 >> 31);
+                            r1 ^= (uint32_t)((int)t1 >> 31);
+                        } else {
+                            const uint32_t idx0 = (base + 32 * m) & (2 * kN - 1);
+                            const uint32_t idx1 = (idx0 + kH) & (2 * kN - 1);
+                            r0 = H[idx0 & (kN - 1)];
+                            r1 = H[idx1 & (kN - 1)];
+                            // negacyclic wrap: -x on the high word is ~x up to the dropped borrow
+                            r0 ^= (uint32_t)((int)(idx0 << 20) >> 31);
+                            r1 ^= (uint32_t)((int)(idx1 << 20) >> 31);
+                        }
                         const double d0 = __int2double_rn(pbs_digit_hi(r0 - own[2 * m]));
                         const double d1 = __int2double_rn(pbs_digit_hi(r1 - own[2 * m + 1]));
                         if (m == 0) {
@@ -586,12 +609,12 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
                         const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
     static bool attr_set = false;
-    static int stagger = 4, opt = 1;   // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1)
+    static int stagger = 4, opt = 5;   // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1)
     if (!attr_set) {
         if (const char *e = getenv("FHS_BR_STAGGER")) stagger = atoi(e);
-        if (const char *e = getenv("FHS_BR_OPT")) opt = atoi(e) & 1;
-#define FHS_BR_ATTR(o, st) FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel<o, st>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem2)))
-        FHS_BR_ATTR(0, 0); FHS_BR_ATTR(1, 3);
+        if (const char *e = getenv("FHS_BR_OPT")) opt = atoi(e) & 5;
+#define FHS_BR_ATTR(o, st) FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel<o, st>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem2Bytes))
+        FHS_BR_ATTR(0, 0); FHS_BR_ATTR(1, 3); FHS_BR_ATTR(5, 3);
 #undef FHS_BR_ATTR
         attr_set = true;
     }
@@ -609,9 +632,10 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
                                 const double2 *, uint64_t *, unsigned int, int, int, uint64_t, int, int);
         // FHS_BR_OPT=0 FHS_BR_STAGGER=0 selects the round-1 baseline kernel (A/B runs); default is
         // the TMEM-twiddle kernel with the stagger flag on (4); 3 = same kernel, flag off.
-        kern_t kern = (opt == 0 && st == 0) ? blind_rotate_v2_kernel<0, 0> : blind_rotate_v2_kernel<1, 3>;
+        kern_t kern = (opt == 0 && st == 0) ? blind_rotate_v2_kernel<0, 0>
+                      : (opt & 4)            ? blind_rotate_v2_kernel<5, 3> : blind_rotate_v2_kernel<1, 3>;
         const int stagger_rt = st == 4;
-        kern<<<(unsigned)ctas, kThreads2, sizeof(Smem2), c->stream>>>(
+        kern<<<(unsigned)ctas, kThreads2, kSmem2Bytes, c->stream>>>(
             d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, (unsigned int)batch,
             (int)c->n, log_box, delta, active, stagger_rt);
     }
