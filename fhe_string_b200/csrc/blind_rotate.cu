@@ -526,7 +526,7 @@ struct XfSmem {
 
 __global__ void __launch_bounds__(32 * kXfWarps)
 bsk_transform_kernel(const uint64_t *__restrict__ bsk, double2 *__restrict__ bsk_f,
-                     const double2 *__restrict__ twiddle_g, int n_polys) {
+                     double2 *__restrict__ bsk_w, const double2 *__restrict__ twiddle_g, int n_polys) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     XfSmem &sm = *reinterpret_cast<XfSmem *>(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -561,8 +561,12 @@ bsk_transform_kernel(const uint64_t *__restrict__ bsk, double2 *__restrict__ bsk
     const double sc = 1.0 / 1024.0 / 17179869184.0;  // 1/1024 (inverse FFT) and 2^-34 (accumulator unit)
 #pragma unroll
     for (int k1 = 0; k1 < 32; k1++) {
-        bsk_f[((((size_t)i * 32 + k1) * 2 + ww) * 32 + lp) * 2 + sl] =
-            make_double2(xr[k1] * sc, xi[k1] * sc);
+        const double2 val = make_double2(xr[k1] * sc, xi[k1] * sc);
+        bsk_f[((((size_t)i * 32 + k1) * 2 + ww) * 32 + lp) * 2 + sl] = val;
+        // wide layout (blind_rotate_wide.cu): frequency K = c + 128 k3, c = q + 64 e; thread
+        // (quarter q >> 4, lane (r << 4) | (q & 15)) holds it in slot f = 8 e + k3
+        const int K = 32 * k1 + k2, cc = K & 127, f = 8 * (cc >> 6) + (K >> 7), qq = cc & 63;
+        bsk_w[((((size_t)i * 16 + f) * 4 + (qq >> 4)) * 32 + ((r << 4) | (qq & 15))) * 2 + sl] = val;
     }
 }
 
@@ -590,7 +594,7 @@ int launch_bsk_transform(Ctx *c, const uint64_t *d_bsk_std) {
     FHS_CUDA(cudaFuncSetAttribute(bsk_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)sizeof(XfSmem)));
     bsk_transform_kernel<<<(n_polys + kXfWarps - 1) / kXfWarps, 32 * kXfWarps, sizeof(XfSmem),
-                           c->stream>>>(d_bsk_std, c->d_bsk_f, c->d_twiddle, n_polys);
+                           c->stream>>>(d_bsk_std, c->d_bsk_f, c->d_bsk_w, c->d_twiddle, n_polys);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     return FHS_OK;
@@ -608,6 +612,14 @@ int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc) {
 int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                         const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
+    {   // small levels: 4 warps per ciphertext (FHS_BR_WIDE=0 disables, =N sets the batch limit)
+        static long wide_limit = -1;
+        if (wide_limit < 0) {
+            const char *e = getenv("FHS_BR_WIDE");
+            wide_limit = e ? atol(e) : 2L * c->sm_count;
+        }
+        if ((long)batch <= wide_limit) return launch_blind_rotate_wide(c, d_small, d_lut_id, d_tables, batch, d_out);
+    }
     static bool attr_set = false;
     static int stagger = 4, opt = 5;   // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1)
     if (!attr_set) {

@@ -60,8 +60,9 @@ static void free_keys(Ctx *c) {
     cudaFree(c->d_ksk_t);
     c->d_ksk_t = nullptr;
     cudaFree(c->d_bsk_f);
+    cudaFree(c->d_bsk_w);
     c->d_ksk = c->d_ksk_corr = nullptr;
-    c->d_bsk_f = nullptr;
+    c->d_bsk_f = c->d_bsk_w = nullptr;
     c->has_keys = false;
 }
 
@@ -223,7 +224,8 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
         if ((e = cudaMalloc(&c->d_ksk, ksk_len * sizeof(uint64_t))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_ksk_corr, (c->n + 1) * sizeof(uint64_t))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_ksk_t, fhs::ksk_tiles_bytes(c))) != cudaSuccess ||
-            (e = cudaMalloc(&c->d_bsk_f, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess) {
+            (e = cudaMalloc(&c->d_bsk_f, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess ||
+            (e = cudaMalloc(&c->d_bsk_w, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "cudaMalloc(keys)");
             break;
         }

@@ -27,6 +27,7 @@ struct Ctx {
     uint8_t *d_ksk_t = nullptr;    // byte-limb tiles of the KSK for the tensor-core keyswitch
     uint64_t *d_ksk_corr = nullptr;// [n+1]  2^(base_log-1) * sum of all KSK rows (unsigned-digit offset)
     double2 *d_bsk_f = nullptr;    // Fourier BSK, layout in blind_rotate.cu
+    double2 *d_bsk_w = nullptr;    // the same values in the layout of blind_rotate_wide.cu
     double2 *d_twiddle = nullptr;  // [32][33] inter-pass twiddles T[k2][n1]
     // scratch
     uint64_t *d_small = nullptr;   // [cap][n+1] keyswitched ciphertexts
@@ -62,6 +63,9 @@ int launch_keyswitch_mma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d
 int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                         const uint64_t *d_tables, size_t batch, uint64_t *d_out);
 int launch_bsk_transform(Ctx *c, const uint64_t *d_bsk_std);
+// blind_rotate_wide.cu: 4 warps per ciphertext, for levels of at most 2 ciphertexts per SM
+int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
+                             const uint64_t *d_tables, size_t batch, uint64_t *d_out);
 int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc);
 size_t bsk_fourier_elems(const Ctx *c);
 
