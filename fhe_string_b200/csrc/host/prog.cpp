@@ -260,7 +260,10 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
     const uint64_t delta = (1ull << 63) / ((uint64_t)prm.message_modulus * prm.carry_modulus);
     const size_t N = g.nodes.size();
     const int D = g.depth();
-    // slots: inputs first, then per level PBS nodes, then the linear outputs of that level
+    auto t_start = std::chrono::steady_clock::now();
+    // ---- plan: slots and descriptor rows of every group, in execution order (host only) ----
+    // slots: inputs first, then per level the PBS nodes, then the linear outputs of that level,
+    // finally the program outputs gathered into consecutive slots (one read-back at the end)
     std::vector<std::vector<int32_t>> pbs_at(D + 1), lin_at(D + 1);
     for (size_t i = 0; i < N; i++) {
         if (g.nodes[i].kind == K_PBS) pbs_at[g.nodes[i].level].push_back((int32_t)i);
@@ -271,66 +274,72 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
     for (size_t i = 0; i < N; i++)
         if (g.nodes[i].kind == K_INPUT) slot[i] = (uint32_t)next++;
     if (next != p->n_inputs) return FHS_ERR_INVALID;
-    fhs_pool *pool = nullptr;
-    if ((rc = fhs_pool_create(ctx, (N ? N : 1) + (size_t)(D + 1) * world, &pool)) != FHS_OK) return rc;
-    auto t_start = std::chrono::steady_clock::now();
-    const uint64_t launches0 = fhs_launch_count(ctx);
-    uint64_t n_pbs = 0, n_levels = 0;
+    struct Grp { size_t row0, rows, out_base, per, lo, hi; bool is_pbs; };
+    std::vector<Grp> groups;
+    std::vector<uint32_t> off{0}, idx, lut;
+    std::vector<int32_t> coef;
+    std::vector<uint64_t> cst;
+    size_t max_rows = 1, n_pbs = 0, n_levels = 0;
+    auto plan_group = [&](const std::vector<int32_t> &ids, bool is_pbs) {
+        if (ids.empty()) return;
+        Grp G{cst.size(), ids.size(), next, 0, 0, ids.size(), is_pbs};
+        for (size_t q = 0; q < ids.size(); q++) {
+            const Node &n = g.nodes[ids[q]];
+            for (uint32_t t = n.t0; t < n.t0 + n.tn; t++) {
+                idx.push_back(slot[g.terms[t].src]);
+                coef.push_back(g.terms[t].coef);
+            }
+            off.push_back((uint32_t)idx.size());
+            cst.push_back((uint64_t)n.c * delta);
+            lut.push_back(is_pbs ? (uint32_t)n.lut : 0u);
+            slot[ids[q]] = (uint32_t)(next + q);
+        }
+        if (is_pbs) {
+            level_slice(ids.size(), rank, world, shard_min, &G.per, &G.lo, &G.hi);
+            max_rows = std::max(max_rows, G.hi - G.lo);
+            n_pbs += ids.size();
+            n_levels++;
+        }
+        next += G.per ? G.per * (size_t)world : ids.size();   // sharded levels are padded to per * world
+        groups.push_back(G);
+    };
+    for (int l = 0; l <= D; l++) { plan_group(pbs_at[l], true); plan_group(lin_at[l], false); }
+    // output gather group: identity rows (or clear constants as trivial ciphertexts)
+    const size_t n_out = p->outputs.size();
+    Grp OG{cst.size(), n_out, next, 0, 0, n_out, false};
+    for (size_t k = 0; k < n_out; k++) {
+        if (p->outputs[k] >= 0) {
+            idx.push_back(slot[p->outputs[k]]);
+            coef.push_back(1);
+            cst.push_back(0);
+        } else {
+            cst.push_back((uint64_t)(-1 - p->outputs[k]) * delta);
+        }
+        off.push_back((uint32_t)idx.size());
+        lut.push_back(0u);
+    }
+    next += n_out;
     std::vector<uint64_t> tables(g.luts.size() * 16);
     for (size_t i = 0; i < g.luts.size(); i++) memcpy(&tables[16 * i], g.luts[i].data(), 16 * sizeof(uint64_t));
+
+    fhs_pool *pool = nullptr;
+    if ((rc = fhs_pool_create(ctx, next ? next : 1, &pool)) != FHS_OK) return rc;
+    const uint64_t launches0 = fhs_launch_count(ctx);
     do {
+        if ((rc = fhs_pool_load_program(pool, cst.size(), idx.size(), off.data(), idx.data(), coef.data(),
+                                        cst.data(), lut.data(), tables.data(), g.luts.size(), max_rows)) != FHS_OK) break;
         if (p->n_inputs && (rc = fhs_pool_write(pool, 0, p->n_inputs, in_blocks)) != FHS_OK) break;
-        std::vector<uint32_t> off, idx, lut;
-        std::vector<int32_t> coef;
-        std::vector<uint64_t> cst;
-        auto run_group = [&](const std::vector<int32_t> &ids, bool is_pbs) -> int {
-            if (ids.empty()) return FHS_OK;
-            off.clear(); idx.clear(); coef.clear(); cst.clear(); lut.clear();
-            off.push_back(0);
-            for (int32_t id : ids) {
-                const Node &n = g.nodes[id];
-                for (uint32_t t = n.t0; t < n.t0 + n.tn; t++) {
-                    idx.push_back(slot[g.terms[t].src]);
-                    coef.push_back(g.terms[t].coef);
-                }
-                off.push_back((uint32_t)idx.size());
-                cst.push_back((uint64_t)n.c * delta);
-                if (is_pbs) lut.push_back((uint32_t)n.lut);
-                slot[id] = (uint32_t)(next + (off.size() - 2));
-            }
-            size_t per = 0, lo = 0, hi = ids.size();
-            if (is_pbs) level_slice(ids.size(), rank, world, shard_min, &per, &lo, &hi);
-            int r = FHS_OK;
-            if (hi > lo) {   // this rank's slice: descriptor rows [lo, hi)
-                std::vector<uint32_t> off2(hi - lo + 1);
-                for (size_t q = lo; q <= hi; q++) off2[q - lo] = off[q] - off[lo];
-                r = fhs_level(pool, hi - lo, off2.data(), idx.data() + off[lo], coef.data() + off[lo],
-                              cst.data() + lo, is_pbs ? lut.data() + lo : nullptr, tables.data(),
-                              g.luts.size(), next + lo);
-            }
-            if (r == FHS_OK && per) {  // exchange result blocks: rank q owns [next + q*per, next + (q+1)*per)
+        for (const Grp &G : groups) {
+            if (G.hi > G.lo && (rc = fhs_level_run(pool, G.row0 + G.lo, G.hi - G.lo, G.is_pbs ? 1 : 0, G.out_base + G.lo)) != FHS_OK) break;
+            if (G.per) {  // exchange result blocks: rank q owns [out_base + q*per, out_base + (q+1)*per)
                 fhs_ctx_synchronize(ctx);
-                if (allgather(user, fhs_pool_device_ptr(pool) + next * width, per * width * sizeof(uint64_t)) != 0) r = FHS_ERR_COMM;
-                next += per * world;   // padded
-            } else {
-                next += ids.size();
+                if (allgather(user, fhs_pool_device_ptr(pool) + G.out_base * width, G.per * width * sizeof(uint64_t)) != 0) { rc = FHS_ERR_COMM; break; }
             }
-            if (is_pbs) { n_pbs += ids.size(); n_levels++; }
-            return r;
-        };
-        for (int l = 0; l <= D && rc == FHS_OK; l++) {
-            if ((rc = run_group(pbs_at[l], true)) != FHS_OK) break;
-            rc = run_group(lin_at[l], false);
         }
         if (rc != FHS_OK) break;
-        for (size_t k = 0; k < p->outputs.size() && rc == FHS_OK; k++) {
-            uint64_t *dst = out_blocks + k * width;
-            if (p->outputs[k] < 0) {  // clear constant -> trivial ciphertext
-                memset(dst, 0, width * sizeof(uint64_t));
-                dst[width - 1] = (uint64_t)(-1 - p->outputs[k]) * delta;
-            } else {
-                rc = fhs_pool_read(pool, slot[p->outputs[k]], 1, dst);
-            }
+        if (n_out) {
+            if ((rc = fhs_level_run(pool, OG.row0, n_out, 0, OG.out_base)) != FHS_OK) break;
+            rc = fhs_pool_read(pool, OG.out_base, n_out, out_blocks);
         }
     } while (0);
     fhs_ctx_synchronize(ctx);

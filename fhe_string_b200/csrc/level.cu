@@ -17,6 +17,11 @@ struct Pool {
     uint64_t *d_cst = nullptr, *d_tables = nullptr;
     size_t cap_b = 0, cap_t = 0, cap_luts = 0;
     uint64_t *d_stage = nullptr;  // [cap_b][big+1] linear-combination results
+    // resident program (fhs_pool_load_program): descriptors of every level, uploaded once
+    uint32_t *r_off = nullptr, *r_idx = nullptr, *r_lut = nullptr;
+    int32_t *r_coef = nullptr;
+    uint64_t *r_cst = nullptr, *r_tables = nullptr, *r_stage = nullptr;
+    size_t r_rows = 0, r_luts = 0, r_max_rows = 0;
 };
 
 namespace {
@@ -98,6 +103,8 @@ void fhs_pool_destroy(fhs_pool *hp) {
     cudaStreamSynchronize(p->ctx->stream);
     cudaFree(p->d); cudaFree(p->d_off); cudaFree(p->d_idx); cudaFree(p->d_lut); cudaFree(p->d_coef);
     cudaFree(p->d_cst); cudaFree(p->d_tables); cudaFree(p->d_stage);
+    cudaFree(p->r_off); cudaFree(p->r_idx); cudaFree(p->r_lut); cudaFree(p->r_coef);
+    cudaFree(p->r_cst); cudaFree(p->r_tables); cudaFree(p->r_stage);
     delete p;
 }
 
@@ -164,6 +171,73 @@ int fhs_level(fhs_pool *hp, size_t B, const uint32_t *term_off, const uint32_t *
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     return fhs_ks_pbs_batch_dev(reinterpret_cast<fhs_ctx *>(c), p->d_stage, p->d_lut, p->d_tables, n_luts, B, dst);
+}
+
+// Resident program: all level descriptors of a level program are uploaded ONCE (rows in execution
+// order, row_off absolute term offsets), so that running a level is kernel launches only -- no
+// host->device descriptor copies and no host synchronisation between the levels of a deep program.
+int fhs_pool_load_program(fhs_pool *hp, size_t rows, size_t terms, const uint32_t *row_off,
+                          const uint32_t *term_idx, const int32_t *term_coef, const uint64_t *const_body,
+                          const uint32_t *lut_id, const uint64_t *lut_tables, size_t n_luts,
+                          size_t max_level_rows) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || !row_off || (terms && (!term_idx || !term_coef)) || (rows && (!const_body || !lut_id)) ||
+        (n_luts && !lut_tables)) return FHS_ERR_INVALID;
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    FHS_CUDA(cudaStreamSynchronize(s));
+    cudaFree(p->r_off); cudaFree(p->r_idx); cudaFree(p->r_lut); cudaFree(p->r_coef);
+    cudaFree(p->r_cst); cudaFree(p->r_tables); cudaFree(p->r_stage);
+    p->r_off = p->r_idx = p->r_lut = nullptr; p->r_coef = nullptr;
+    p->r_cst = p->r_tables = p->r_stage = nullptr;
+    p->r_rows = 0;
+    const size_t w = (size_t)c->big + 1;
+    FHS_CUDA(cudaMalloc(&p->r_off, (rows + 1) * sizeof(uint32_t)));
+    FHS_CUDA(cudaMalloc(&p->r_idx, (terms + 1) * sizeof(uint32_t)));
+    FHS_CUDA(cudaMalloc(&p->r_coef, (terms + 1) * sizeof(int32_t)));
+    FHS_CUDA(cudaMalloc(&p->r_cst, (rows + 1) * sizeof(uint64_t)));
+    FHS_CUDA(cudaMalloc(&p->r_lut, (rows + 1) * sizeof(uint32_t)));
+    FHS_CUDA(cudaMalloc(&p->r_tables, (n_luts + 1) * c->space * sizeof(uint64_t)));
+    FHS_CUDA(cudaMalloc(&p->r_stage, (max_level_rows + 1) * w * sizeof(uint64_t)));
+    FHS_CUDA(cudaMemcpyAsync(p->r_off, row_off, (rows + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+    if (terms) {
+        FHS_CUDA(cudaMemcpyAsync(p->r_idx, term_idx, terms * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+        FHS_CUDA(cudaMemcpyAsync(p->r_coef, term_coef, terms * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    }
+    if (rows) {
+        FHS_CUDA(cudaMemcpyAsync(p->r_cst, const_body, rows * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
+        FHS_CUDA(cudaMemcpyAsync(p->r_lut, lut_id, rows * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
+    }
+    if (n_luts)
+        FHS_CUDA(cudaMemcpyAsync(p->r_tables, lut_tables, n_luts * c->space * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
+    FHS_CUDA(cudaStreamSynchronize(s));   // host arrays may be freed by the caller
+    p->r_rows = rows; p->r_luts = n_luts; p->r_max_rows = max_level_rows;
+    return FHS_OK;
+}
+
+// Rows [row_lo, row_lo + B) of the resident program -> pool slots [out_slot, out_slot + B).
+// Asynchronous on the context's stream.
+int fhs_level_run(fhs_pool *hp, size_t row_lo, size_t B, int is_pbs, size_t out_slot) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p) return FHS_ERR_INVALID;
+    if (B == 0) return FHS_OK;
+    Ctx *c = p->ctx;
+    if (row_lo + B > p->r_rows || out_slot + B > p->capacity || (is_pbs && (B > p->r_max_rows || !p->r_luts))) {
+        fhs::set_error("fhs_level_run: rows [%zu, %zu) of %zu, out_slot %zu, capacity %zu", row_lo, row_lo + B,
+                       p->r_rows, out_slot, p->capacity);
+        return FHS_ERR_INVALID;
+    }
+    FHS_CUDA(cudaSetDevice(c->device));
+    const int width = (int)c->big + 1;
+    uint64_t *dst = p->d + out_slot * (size_t)width;
+    fhs::gather_linear_kernel<<<(unsigned)B, 256, 0, c->stream>>>(p->d, p->r_off + row_lo, p->r_idx, p->r_coef,
+                                                                   p->r_cst + row_lo, is_pbs ? p->r_stage : dst, width);
+    c->launches++;
+    FHS_CUDA(cudaGetLastError());
+    if (!is_pbs) return FHS_OK;
+    return fhs_ks_pbs_batch_dev(reinterpret_cast<fhs_ctx *>(c), p->r_stage, p->r_lut + row_lo, p->r_tables,
+                                p->r_luts, B, dst);
 }
 
 }  // extern "C"

@@ -135,6 +135,17 @@ int fhs_level(fhs_pool *pool, size_t B, const uint32_t *term_off, const uint32_t
               const int32_t *term_coef, const uint64_t *const_body, const uint32_t *lut_id,
               const uint64_t *lut_tables, size_t n_luts, size_t out_slot);
 
+/* Resident level program: upload the descriptors of EVERY level of a program once (rows in
+ * execution order; row_off[rows+1] are absolute offsets into term_idx / term_coef; lut_id is ignored
+ * for rows that are run with is_pbs = 0), then run levels with kernel launches only.  This is what
+ * the level scheduler (include/fhs_string.h) uses: a 71-level split costs 71 x 3 launches and no
+ * host<->device traffic between its first input block and its last output block. */
+int fhs_pool_load_program(fhs_pool *pool, size_t rows, size_t terms, const uint32_t *row_off,
+                          const uint32_t *term_idx, const int32_t *term_coef, const uint64_t *const_body,
+                          const uint32_t *lut_id, const uint64_t *lut_tables, size_t n_luts,
+                          size_t max_level_rows);
+int fhs_level_run(fhs_pool *pool, size_t row_lo, size_t B, int is_pbs, size_t out_slot);
+
 #ifdef __cplusplus
 }
 #endif
