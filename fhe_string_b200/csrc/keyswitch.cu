@@ -179,7 +179,9 @@ int launch_keyswitch(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_sma
     // large levels: integer tensor cores (keyswitch_mma.cu); FHS_KS_VARIANT=1 forces the IMAD kernel
     static int variant = -1;
     if (variant < 0) { const char *e = getenv("FHS_KS_VARIANT"); variant = e ? atoi(e) : 2; }
-    if (variant == 2 && batch >= 24) return launch_keyswitch_mma(c, d_in, batch, d_small);
+    static int mma_min = -1;
+    if (mma_min < 0) { const char *e = getenv("FHS_KS_MMA_MIN"); mma_min = e ? atoi(e) : 1; }
+    if (variant == 2 && batch >= (size_t)mma_min) return launch_keyswitch_mma(c, d_in, batch, d_small);
     // tile size: fill the SMs first, then grow tiles up to kKsTb (KSK traffic ~ 1/tile)
     int per = (int)((batch + c->sm_count - 1) / c->sm_count);
     if (per < 1) per = 1;

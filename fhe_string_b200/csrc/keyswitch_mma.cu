@@ -47,7 +47,11 @@ __device__ __forceinline__ void mma_s8u8(int (&c)[4], const uint32_t (&a)[4], co
 
 __global__ void __launch_bounds__(kThreadsM, 1)
 keyswitch_mma_kernel(const uint64_t *__restrict__ in, const uint8_t *__restrict__ kt,
-                     uint64_t *__restrict__ out, unsigned int batch, int n_small, int big, int n_kb) {
+                     uint64_t *__restrict__ out, unsigned int batch, int n_small, int big, int n_kb_total) {
+    // split-K over blockIdx.z (small batches: fill the SMs; partial sums are combined with u64
+    // atomics into a zeroed output, the body term is added by the first slice)
+    const int kb_base = (int)(((long long)blockIdx.z * n_kb_total) / gridDim.z);
+    const int n_kb = (int)(((long long)(blockIdx.z + 1) * n_kb_total) / gridDim.z) - kb_base;
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char *Bs = smem;                       // 2 stages
     unsigned char *As = smem + 2 * kStageBytes;     // 2 stages
@@ -58,7 +62,7 @@ keyswitch_mma_kernel(const uint64_t *__restrict__ in, const uint8_t *__restrict_
     const unsigned int m0 = blockIdx.y * kMT;
     const int n_tile = blockIdx.x;
     const size_t in_w = (size_t)big + 1;
-    const unsigned char *kt_tile = kt + (size_t)n_tile * n_kb * kStageBytes;
+    const unsigned char *kt_tile = kt + ((size_t)n_tile * n_kb_total + kb_base) * kStageBytes;
 
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mbar[0])));
@@ -82,7 +86,7 @@ keyswitch_mma_kernel(const uint64_t *__restrict__ in, const uint8_t *__restrict_
             const int q = tid + kThreadsM * r, b = q >> 3, i4 = (q & 7) * 4;
             const unsigned int ct = m0 + b;
             if (ct < batch) {
-                const uint64_t *p = in + (size_t)ct * in_w + (size_t)kb * kKI + i4;
+                const uint64_t *p = in + (size_t)ct * in_w + (size_t)(kb_base + kb) * kKI + i4;
 #pragma unroll
                 for (int e = 0; e < 4; e++) pre[r][e] = __ldg(p + e);
             } else {
@@ -180,8 +184,10 @@ keyswitch_mma_kernel(const uint64_t *__restrict__ in, const uint8_t *__restrict_
                 v += __shfl_xor_sync(0xffffffffu, v, 2);
                 const unsigned int ct = m0 + wm * 64 + mi * 16 + g + 8 * h;
                 if (tg == 0 && ct < batch && j < out_w) {
-                    const uint64_t body = (j == n_small) ? in[(size_t)ct * in_w + big] : 0ull;
-                    out[(size_t)ct * out_w + j] = body - v;
+                    const uint64_t body = (j == n_small && blockIdx.z == 0) ? in[(size_t)ct * in_w + big] : 0ull;
+                    if (gridDim.z == 1) out[(size_t)ct * out_w + j] = body - v;
+                    else atomicAdd(reinterpret_cast<unsigned long long *>(out + (size_t)ct * out_w + j),
+                                   (unsigned long long)(body - v));
                 }
             }
         }
@@ -235,7 +241,12 @@ int launch_keyswitch_mma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d
         attr = true;
     }
     const int n_tiles = (int)(((size_t)(c->n + 1) * 8 + kNT - 1) / kNT);
-    dim3 grid(n_tiles, (unsigned)((batch + kMT - 1) / kMT));
+    const unsigned m_tiles = (unsigned)((batch + kMT - 1) / kMT);
+    unsigned ksplit = 1;
+    while (ksplit < 8 && n_tiles * m_tiles * (ksplit + 1) <= (unsigned)c->sm_count) ksplit++;
+    if (ksplit > 1)
+        FHS_CUDA(cudaMemsetAsync(d_small, 0, batch * ((size_t)c->n + 1) * sizeof(uint64_t), c->stream));
+    dim3 grid(n_tiles, m_tiles, ksplit);
     keyswitch_mma_kernel<<<grid, kThreadsM, smem_bytes, c->stream>>>(d_in, c->d_ksk_t, d_small, (unsigned int)batch,
                                                                       (int)c->n, (int)c->big, (int)(c->big / kKI));
     c->launches++;
