@@ -355,14 +355,15 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
 
 // ------------------------------------------------------------------------------------------------
 // Batched executor: M independent instances of one program (e.g. 1024 string comparisons, BASELINE
-// config 5).  Every level becomes M * B_level LUT evaluations, issued in chunks of at most
-// kManyChunk evaluations per fhs_level call, so small per-instance levels still fill the GPU.
-// Pool layout: inputs [m][n_inputs]; group of node ids at base b: [m][ids.size()].
+// config 5).  Instances are processed in chunks of Mc; within a chunk every level is ONE fhs_level_run
+// over Mc * B_level evaluations (resident descriptors, generated once: slots are relative to the pool),
+// and two pools are used in turn so that the H2D upload of chunk c+1 (side stream) overlaps with the
+// levels of chunk c.  Pool layout: inputs [m][n_inputs]; group of node ids at base b: [m][ids.size()].
 extern "C" int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_instances,
                                  const uint64_t *in_blocks, uint64_t *out_blocks, double stats[4]) {
     if (!p || !ctx || (!in_blocks && p->n_inputs) || !out_blocks) return FHS_ERR_INVALID;
     if (n_instances == 0) return FHS_OK;
-    constexpr size_t kManyChunk = 32768;
+    constexpr size_t kManyChunk = 24576;    // target LUT evaluations of the largest level of a chunk
     const size_t M = n_instances;
     const Graph &g = p->g;
     fhs_params prm;
@@ -372,91 +373,109 @@ extern "C" int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_insta
     const uint64_t delta = (1ull << 63) / ((uint64_t)prm.message_modulus * prm.carry_modulus);
     const size_t N = g.nodes.size();
     const int D = g.depth();
+    auto t_start = std::chrono::steady_clock::now();
     std::vector<std::vector<int32_t>> pbs_at(D + 1), lin_at(D + 1);
+    size_t gmax = 1;
     for (size_t i = 0; i < N; i++) {
         if (g.nodes[i].kind == K_PBS) pbs_at[g.nodes[i].level].push_back((int32_t)i);
         else if (g.nodes[i].kind == K_LIN) lin_at[g.nodes[i].level].push_back((int32_t)i);
     }
-    // slot of (node, instance m) = base[node] + m * stride[node]
+    for (auto &v : pbs_at) gmax = std::max(gmax, v.size());
+    const size_t Mc = std::max<size_t>(1, std::min(M, kManyChunk / gmax));
+    // ---- plan for one chunk of Mc instances: slot(node, m) = base[node] + m * stride[node] ----
     std::vector<size_t> base(N, 0), stride(N, 0);
     size_t n_in = 0;
     for (size_t i = 0; i < N; i++)
-        if (g.nodes[i].kind == K_INPUT) { base[i] = n_in++; }
+        if (g.nodes[i].kind == K_INPUT) base[i] = n_in++;
     if (n_in != p->n_inputs) return FHS_ERR_INVALID;
     for (size_t i = 0; i < N; i++)
         if (g.nodes[i].kind == K_INPUT) stride[i] = n_in;
-    size_t next = n_in * M;
-    if ((N ? N : 1) * M >= (1ull << 32)) { return FHS_ERR_INVALID; }
-    fhs_pool *pool = nullptr;
-    if ((rc = fhs_pool_create(ctx, (N ? N : 1) * M, &pool)) != FHS_OK) return rc;
-    auto t_start = std::chrono::steady_clock::now();
-    const uint64_t launches0 = fhs_launch_count(ctx);
-    uint64_t n_pbs = 0, n_levels = 0;
+    const size_t n_out = p->outputs.size();
+    if ((N + n_out + 1) * Mc >= (1ull << 32)) return FHS_ERR_INVALID;
+    struct Grp { size_t row0, rows, out_base; bool is_pbs; };
+    std::vector<Grp> groups;
+    std::vector<uint32_t> off{0}, idx, lut;
+    std::vector<int32_t> coef;
+    std::vector<uint64_t> cst;
+    size_t next = n_in * Mc, max_rows = 1, pbs_per_instance = 0, n_levels = 0;
+    auto plan_group = [&](const std::vector<int32_t> &ids, bool is_pbs) {
+        if (ids.empty()) return;
+        const size_t G = ids.size();
+        groups.push_back(Grp{cst.size(), G * Mc, next, is_pbs});
+        for (size_t m = 0; m < Mc; m++) {
+            for (int32_t id : ids) {
+                const Node &n = g.nodes[id];
+                for (uint32_t t = n.t0; t < n.t0 + n.tn; t++) {
+                    const int32_t src = g.terms[t].src;
+                    idx.push_back((uint32_t)(base[src] + m * stride[src]));
+                    coef.push_back(g.terms[t].coef);
+                }
+                off.push_back((uint32_t)idx.size());
+                cst.push_back((uint64_t)n.c * delta);
+                lut.push_back(is_pbs ? (uint32_t)n.lut : 0u);
+            }
+        }
+        for (size_t q = 0; q < G; q++) { base[ids[q]] = next + q; stride[ids[q]] = G; }
+        next += G * Mc;
+        if (is_pbs) { max_rows = std::max(max_rows, G * Mc); pbs_per_instance += G; n_levels++; }
+    };
+    for (int l = 0; l <= D; l++) { plan_group(pbs_at[l], true); plan_group(lin_at[l], false); }
+    // output gather: [m][n_out] consecutive slots -> one read-back per chunk
+    Grp OG{cst.size(), n_out * Mc, next, false};
+    for (size_t m = 0; m < Mc; m++) {
+        for (size_t k = 0; k < n_out; k++) {
+            if (p->outputs[k] >= 0) {
+                const size_t node = (size_t)p->outputs[k];
+                idx.push_back((uint32_t)(base[node] + m * stride[node]));
+                coef.push_back(1);
+                cst.push_back(0);
+            } else {
+                cst.push_back((uint64_t)(-1 - p->outputs[k]) * delta);
+            }
+            off.push_back((uint32_t)idx.size());
+            lut.push_back(0u);
+        }
+    }
+    next += n_out * Mc;
     std::vector<uint64_t> tables(g.luts.size() * 16);
     for (size_t i = 0; i < g.luts.size(); i++) memcpy(&tables[16 * i], g.luts[i].data(), 16 * sizeof(uint64_t));
+
+    const size_t n_chunks = (M + Mc - 1) / Mc;
+    fhs_pool *pool[2] = {nullptr, nullptr};
+    const uint64_t launches0 = fhs_launch_count(ctx);
     do {
-        if (n_in && (rc = fhs_pool_write(pool, 0, n_in * M, in_blocks)) != FHS_OK) break;
-        std::vector<uint32_t> off, idx, lut;
-        std::vector<int32_t> coef;
-        std::vector<uint64_t> cst;
-        auto run_group = [&](const std::vector<int32_t> &ids, bool is_pbs) -> int {
-            if (ids.empty()) return FHS_OK;
-            const size_t G = ids.size();
-            for (size_t q = 0; q < G; q++) { base[ids[q]] = next + q; stride[ids[q]] = G; }
-            const size_t inst_per_call = std::max<size_t>(1, kManyChunk / G);
-            int r = FHS_OK;
-            for (size_t m0 = 0; m0 < M && r == FHS_OK; m0 += inst_per_call) {
-                const size_t m1 = std::min(M, m0 + inst_per_call);
-                off.clear(); idx.clear(); coef.clear(); cst.clear(); lut.clear();
-                off.push_back(0);
-                for (size_t m = m0; m < m1; m++) {
-                    for (int32_t id : ids) {
-                        const Node &n = g.nodes[id];
-                        for (uint32_t t = n.t0; t < n.t0 + n.tn; t++) {
-                            const int32_t src = g.terms[t].src;
-                            idx.push_back((uint32_t)(base[src] + m * stride[src]));
-                            coef.push_back(g.terms[t].coef);
-                        }
-                        off.push_back((uint32_t)idx.size());
-                        cst.push_back((uint64_t)n.c * delta);
-                        if (is_pbs) lut.push_back((uint32_t)n.lut);
-                    }
-                }
-                r = fhs_level(pool, (m1 - m0) * G, off.data(), idx.data(), coef.data(), cst.data(),
-                              is_pbs ? lut.data() : nullptr, tables.data(), g.luts.size(), next + m0 * G);
-                // descriptor vectors are reused by the next chunk: wait until the copies were consumed
-                if (r == FHS_OK && m1 < M) fhs_ctx_synchronize(ctx);
-            }
-            next += G * M;
-            if (is_pbs) { n_pbs += G * M; n_levels++; }
-            return r;
-        };
-        for (int l = 0; l <= D && rc == FHS_OK; l++) {
-            if ((rc = run_group(pbs_at[l], true)) != FHS_OK) break;
-            rc = run_group(lin_at[l], false);
+        for (int b = 0; b < (n_chunks > 1 ? 2 : 1) && rc == FHS_OK; b++) {
+            if ((rc = fhs_pool_create(ctx, next ? next : 1, &pool[b])) != FHS_OK) break;
+            rc = fhs_pool_load_program(pool[b], cst.size(), idx.size(), off.data(), idx.data(), coef.data(), cst.data(),
+                                       lut.data(), tables.data(), g.luts.size(), max_rows);
         }
         if (rc != FHS_OK) break;
-        const size_t n_out = p->outputs.size();
-        for (size_t m = 0; m < M && rc == FHS_OK; m++) {
-            for (size_t k = 0; k < n_out && rc == FHS_OK; k++) {
-                uint64_t *dst = out_blocks + (m * n_out + k) * width;
-                if (p->outputs[k] < 0) {
-                    memset(dst, 0, width * sizeof(uint64_t));
-                    dst[width - 1] = (uint64_t)(-1 - p->outputs[k]) * delta;
-                } else {
-                    const size_t node = (size_t)p->outputs[k];
-                    rc = fhs_pool_read(pool, base[node] + m * stride[node], 1, dst);
-                }
-            }
+        auto upload = [&](size_t c) -> int {   // inputs of chunk c -> its pool, on the side stream
+            const size_t m0 = c * Mc, mc = std::min(Mc, M - m0);
+            return n_in ? fhs_pool_write_async(pool[c & 1], 0, n_in * mc, in_blocks + m0 * n_in * width) : FHS_OK;
+        };
+        if ((rc = upload(0)) != FHS_OK) break;
+        for (size_t c = 0; c < n_chunks && rc == FHS_OK; c++) {
+            fhs_pool *P = pool[c & 1];
+            const size_t m0 = c * Mc, mc = std::min(Mc, M - m0);
+            if ((rc = fhs_pool_wait_writes(P)) != FHS_OK) break;
+            // a short last chunk runs the same rows; instances >= mc compute on stale inputs and are ignored
+            for (const Grp &G : groups)
+                if ((rc = fhs_level_run(P, G.row0, G.rows, G.is_pbs ? 1 : 0, G.out_base)) != FHS_OK) break;
+            if (rc != FHS_OK) break;
+            if (n_out && (rc = fhs_level_run(P, OG.row0, OG.rows, 0, OG.out_base)) != FHS_OK) break;
+            if (c + 1 < n_chunks && (rc = upload(c + 1)) != FHS_OK) break;   // overlaps with the levels above
+            if (n_out) rc = fhs_pool_read(P, OG.out_base, n_out * mc, out_blocks + m0 * n_out * width);
         }
     } while (0);
     fhs_ctx_synchronize(ctx);
     if (stats) {
         stats[0] = (double)n_levels;
-        stats[1] = (double)n_pbs;
+        stats[1] = (double)(pbs_per_instance * M);
         stats[2] = (double)(fhs_launch_count(ctx) - launches0);
         stats[3] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
     }
-    fhs_pool_destroy(pool);
+    fhs_pool_destroy(pool[0]);
+    fhs_pool_destroy(pool[1]);
     return rc;
 }

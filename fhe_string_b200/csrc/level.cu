@@ -22,6 +22,10 @@ struct Pool {
     int32_t *r_coef = nullptr;
     uint64_t *r_cst = nullptr, *r_tables = nullptr, *r_stage = nullptr;
     size_t r_rows = 0, r_luts = 0, r_max_rows = 0;
+    // side-stream uploads (fhs_pool_write_async): overlap the next batch's H2D with this batch's levels
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t write_done = nullptr;
+    bool write_pending = false;
 };
 
 namespace {
@@ -105,6 +109,8 @@ void fhs_pool_destroy(fhs_pool *hp) {
     cudaFree(p->d_cst); cudaFree(p->d_tables); cudaFree(p->d_stage);
     cudaFree(p->r_off); cudaFree(p->r_idx); cudaFree(p->r_lut); cudaFree(p->r_coef);
     cudaFree(p->r_cst); cudaFree(p->r_tables); cudaFree(p->r_stage);
+    if (p->copy_stream) { cudaStreamSynchronize(p->copy_stream); cudaStreamDestroy(p->copy_stream); }
+    if (p->write_done) cudaEventDestroy(p->write_done);
     delete p;
 }
 
@@ -171,6 +177,36 @@ int fhs_level(fhs_pool *hp, size_t B, const uint32_t *term_off, const uint32_t *
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     return fhs_ks_pbs_batch_dev(reinterpret_cast<fhs_ctx *>(c), p->d_stage, p->d_lut, p->d_tables, n_luts, B, dst);
+}
+
+// Upload on a side stream: returns once the host buffer has been consumed (pageable memory is staged
+// by the runtime), the DMA itself overlaps with kernels already queued on the context's stream.
+// fhs_pool_wait_writes makes the context's stream wait for it.  The caller guarantees that no
+// kernel still reads or writes the target slots (e.g. it has read back the previous results).
+int fhs_pool_write_async(fhs_pool *hp, size_t slot, size_t n, const uint64_t *host_blocks) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || (!host_blocks && n) || slot + n > p->capacity) { fhs::set_error("pool write out of range"); return FHS_ERR_INVALID; }
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    if (!p->copy_stream) {
+        FHS_CUDA(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
+        FHS_CUDA(cudaEventCreateWithFlags(&p->write_done, cudaEventDisableTiming));
+    }
+    const size_t w = (size_t)c->big + 1;
+    FHS_CUDA(cudaMemcpyAsync(p->d + slot * w, host_blocks, n * w * sizeof(uint64_t), cudaMemcpyHostToDevice, p->copy_stream));
+    FHS_CUDA(cudaEventRecord(p->write_done, p->copy_stream));
+    p->write_pending = true;
+    return FHS_OK;
+}
+
+int fhs_pool_wait_writes(fhs_pool *hp) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p) return FHS_ERR_INVALID;
+    if (!p->write_pending) return FHS_OK;
+    FHS_CUDA(cudaSetDevice(p->ctx->device));
+    FHS_CUDA(cudaStreamWaitEvent(p->ctx->stream, p->write_done, 0));
+    p->write_pending = false;
+    return FHS_OK;
 }
 
 // Resident program: all level descriptors of a level program are uploaded ONCE (rows in execution

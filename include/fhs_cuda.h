@@ -135,6 +135,12 @@ int fhs_level(fhs_pool *pool, size_t B, const uint32_t *term_off, const uint32_t
               const int32_t *term_coef, const uint64_t *const_body, const uint32_t *lut_id,
               const uint64_t *lut_tables, size_t n_luts, size_t out_slot);
 
+/* Side-stream upload into a pool (overlaps with levels already queued on the context's stream) and
+ * the matching wait of the context's stream.  Used by fhs_prog_run_many to hide the H2D of the next
+ * chunk of instances behind the levels of the current one. */
+int fhs_pool_write_async(fhs_pool *pool, size_t slot, size_t n, const uint64_t *host_blocks);
+int fhs_pool_wait_writes(fhs_pool *pool);
+
 /* Resident level program: upload the descriptors of EVERY level of a program once (rows in
  * execution order; row_off[rows+1] are absolute offsets into term_idx / term_coef; lut_id is ignored
  * for rows that are run with is_pbs = 0), then run levels with kernel launches only.  This is what
