@@ -188,6 +188,30 @@ class FheStringSliceVector:
     def __init__(self, s, entries):
         self.s, self.v = s, entries
 
+    def _blocks(self):
+        parts = [self.s.blocks]
+        for is_some, start, end in self.v:
+            parts += [is_some.blocks, start.blocks, end.blocks]
+        return np.concatenate(parts)
+
+    def _run(self, k, op, extra=()):
+        key = (op, self.s.n_chars, len(self.v))
+        p = k._progs.get(key)
+        if p is None:
+            p = Program(op, [self.s.n_chars], 0, (len(self.v),), k.num_blocks_char, k.num_blocks_usize)
+            k._progs[key] = p
+        inb = np.concatenate([self._blocks()] + [e.blocks for e in extra])
+        out, k.last_stats = p.run(k.engine, inb)
+        return _wrap(p.desc, out, k.num_blocks_usize)
+
+    def len(self, k):
+        """split.rs:32: number of substrings (encrypted)."""
+        return self._run(k, "slices_len")
+
+    def get(self, k, i):
+        """split.rs:46: the substring at encrypted index i, if existent."""
+        return self._run(k, "slices_get", [i])
+
     def decrypt(self, k):
         s = self.s.decrypt(k)
         out = []

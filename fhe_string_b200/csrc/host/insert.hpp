@@ -104,6 +104,31 @@ struct InsertOps : ReplaceOps {
         if (!have) { acc.max_len = 0; acc.len = usize(0); }
         return str_of(acc, l);
     }
+
+    // ---- FheStringSliceVector::len / get (split.rs:32-83) ----
+    // number of present pieces: sum of the is_some flags (chunks of 3 bools fit a digit, then radix adds)
+    Rad slices_len(const FSliceVec &sv) {
+        Rad acc = usize(0);
+        for (auto &e : sv.v) acc = inc_if(acc, e.is_some);
+        return acc;
+    }
+    // the i-th present piece: one-hot over the entries by (is_some_j && #present before j == i)
+    FOptStr slices_get(const FSliceVec &sv, const Rad &i) {
+        Rad n = usize(0);
+        std::vector<Bool> hit;
+        std::vector<Rad> st, en;
+        for (auto &e : sv.v) {
+            Bool sel = band(e.is_some, Ops::eq(i, n));
+            hit.push_back(sel);
+            st.push_back(select_zero(sel, e.start));
+            en.push_back(select_zero(sel, e.end));
+            n = inc_if(n, e.is_some);
+        }
+        Rad start = onehot_sum(st, nb_usize), end = onehot_sum(en, nb_usize);
+        // mod.rs substr_end(start, end) = chars [start, end): keep i < end, then shift left by start
+        FStr piece = shift_left(substr_to(sv.s, end), start);
+        return FOptStr{any(hit), piece};
+    }
 };
 
 }  // namespace fhs_host

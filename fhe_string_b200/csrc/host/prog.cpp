@@ -57,6 +57,21 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
     }
     std::vector<Rad> U;
     for (size_t i = 0; i < n_usize_args; i++) U.push_back(B.in_usize());
+    // slices_len / slices_get take a FheStringSliceVector exactly as split* returns it: the string,
+    // then scalars[0] entries of (is_some, start, end); slices_get is followed by the index usize.
+    FSliceVec SV;
+    if (op == "slices_len" || op == "slices_get") {
+        if (n_strings != 1 || n_usize_args != 0 || n_scalars < 1) { g_host_err = "wrong operand count for op " + op; return FHS_ERR_INVALID; }
+        SV.s = S[0];
+        for (uint64_t e = 0; e < scalars[0]; e++) {
+            FSlice sl;
+            sl.is_some = B.P.g.input(1);
+            sl.start = B.in_usize();
+            sl.end = B.in_usize();
+            SV.v.push_back(sl);
+        }
+        if (op == "slices_get") U.push_back(B.in_usize());
+    }
     B.P.n_inputs = B.P.g.nodes.size();
     auto need = [&](size_t ns, size_t nu) { return n_strings == ns && n_usize_args == nu; };
     auto bad = [&]() { g_host_err = "wrong operand count for op " + op; return FHS_ERR_INVALID; };
@@ -126,6 +141,11 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
         size_t l = (size_t)std::min<uint64_t>(scalars[0], maxlen);
         FStr r = op == "replace" ? o.replace(S[0], S[1], S[2], l) : o.replacen(S[0], S[1], S[2], U[0], l);
         B.out_str(r); B.P.desc = str_desc(r);
+    }
+    else if (op == "slices_len") { B.out_rad(o.slices_len(SV)); B.P.desc = "usize"; }
+    else if (op == "slices_get") {
+        FOptStr r = o.slices_get(SV, U[0]);
+        B.out_lin(r.is_some); B.out_str(r.val); B.P.desc = "opt_" + str_desc(r.val);
     }
     else if (op == "add") {           // insert.rs:14  operands: a, b
         if (!need(2, 0)) return bad();

@@ -189,3 +189,21 @@ def test_repeat(a, pa):
     for n in (0, 1, 2, 3, 5, 8, 20):
         for l in (0, 1, 4, 7, 16):
             assert run("repeat", [a], [pa], usizes=[n], scalars=(l,)) == (a * n)[:l]
+
+
+def test_slice_vector_len_and_get():
+    """FheStringSliceVector::len / get (split.rs:32-83) chained after split: the split program's
+    output blocks are the input of slices_len / slices_get."""
+    for s, pat in ((" A bcbc ", "bc"), ("a,b,,c", ","), ("xxx", "x"), ("abc", "zz")):
+        chars = [enc_chars(s, 9), enc_chars(pat)]
+        sp = Program("split", [len(c) for c in chars], 0, (), 4, 4)
+        vals = eval_clear(sp.export(), [b for c in chars for b in to_blocks(c)])
+        n_entries = int(sp.desc.split(":")[1])
+        want = s.split(pat)
+        ln = Program("slices_len", [len(chars[0])], 0, (n_entries,), 4, 4)
+        assert decode(ln.desc, eval_clear(ln.export(), vals)) == len(want)
+        gt = Program("slices_get", [len(chars[0])], 0, (n_entries,), 4, 4)
+        ex = gt.export()
+        for i in range(len(want) + 2):
+            got = decode(gt.desc, eval_clear(ex, vals + usize_blocks(i)))
+            assert got == (want[i] if i < len(want) else None), (s, pat, i, got)

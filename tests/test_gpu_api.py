@@ -29,6 +29,13 @@ def test_api_roundtrip_and_ops(keys):
     assert s.strip_prefix(sk, ck.encrypt_str("Hello")).decrypt(ck) == ", B200!"
     assert s.strip_prefix(sk, p).decrypt(ck) is None
     assert s.substr_from(sk, ck.encrypt_usize(7)).decrypt(ck) == "B200!"
+    # insert.rs + FheStringSliceVector::len / get (split.rs:32-83)
+    assert s.add(sk, p).decrypt(ck) == "Hello, B200!B2"
+    assert p.repeat(sk, ck.encrypt_usize(3), 6).decrypt(ck) == "B2B2B2"
+    sv = s.split(sk, ck.encrypt_str("l"))
+    assert sv.len(sk).decrypt(ck) == 3
+    assert sv.get(sk, ck.encrypt_usize(2)).decrypt(ck) == "o, B200!"
+    assert sv.get(sk, ck.encrypt_usize(5)).decrypt(ck) is None
 
 
 def test_cmd_driver_all_equal():
