@@ -232,11 +232,13 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
 // Executor: level by level on a device-resident pool (fhs_pool / fhs_level of include/fhs_cuda.h).
 #include <chrono>
 
-// Slice of a level of B evaluations owned by `rank`: levels below shard_min * world evaluations are
-// computed redundantly by every rank (one blind-rotation wave costs the same for 1 or 148
-// ciphertexts, so splitting them only adds an exchange).
+// Slice of a level of B evaluations owned by `rank`.  A level of at most shard_min evaluations (148 =
+// one wave of the wide blind-rotation kernel, 2.3 ms however few ciphertexts it has) is computed
+// redundantly by every rank; anything larger is split, because ceil(B / world) ciphertexts per GPU
+// finish sooner than B on one GPU even after the all-gather (B = 592: 6.2 ms on one GPU, 2.3 ms +
+// exchange on four).
 static void level_slice(size_t B, int rank, int world, size_t shard_min, size_t *per, size_t *lo, size_t *hi) {
-    if (world <= 1 || B < shard_min * (size_t)world) { *per = 0; *lo = 0; *hi = B; return; }
+    if (world <= 1 || B <= shard_min) { *per = 0; *lo = 0; *hi = B; return; }
     *per = (B + world - 1) / world;
     *lo = std::min(B, *per * (size_t)rank);
     *hi = std::min(B, *per * (size_t)(rank + 1));
