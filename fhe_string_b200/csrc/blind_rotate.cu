@@ -630,15 +630,18 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
                                             d_out + head * ((size_t)c->big + 1));
         }
     }
-    static bool attr_set = false;
+    static bool knobs_read = false;
     static int stagger = 4, opt = 5;   // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1)
-    if (!attr_set) {
+    if (!knobs_read) {
+        knobs_read = true;
         if (const char *e = getenv("FHS_BR_STAGGER")) stagger = atoi(e);
         if (const char *e = getenv("FHS_BR_OPT")) opt = atoi(e) & 5;
+    }
+    if (!c->attr_br) {
 #define FHS_BR_ATTR(o, st) FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel<o, st>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem2Bytes))
         FHS_BR_ATTR(0, 0); FHS_BR_ATTR(1, 3); FHS_BR_ATTR(5, 3);
 #undef FHS_BR_ATTR
-        attr_set = true;
+        c->attr_br = true;
     }
     const int log_box = ilog2(kN / c->space);
     const uint64_t delta = (1ull << 63) / c->space;

@@ -397,11 +397,10 @@ int w_ilog2(uint32_t x) {
 int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                              const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!c->attr_brw) {
         FHS_CUDA(cudaFuncSetAttribute(blind_rotate_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)kWSmemBytes));
-        attr_set = true;
+        c->attr_brw = true;
     }
     const int log_box = w_ilog2(kN / c->space);
     const uint64_t delta = (1ull << 63) / c->space;

@@ -41,6 +41,8 @@ struct Ctx {
     bool ev_valid[2] = {false, false};
     uint64_t launches = 0;
     int sm_count = 0;
+    // cudaFuncSetAttribute is per device: done once per context, not once per process
+    bool attr_br = false, attr_brw = false, attr_ks = false;
 };
 
 void set_error(const char *fmt, ...);

@@ -234,11 +234,10 @@ int launch_ksk_tile(Ctx *c) {
 }
 
 int launch_keyswitch_mma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_small) {
-    static bool attr = false;
     const int smem_bytes = 4 * kStageBytes;
-    if (!attr) {
+    if (!c->attr_ks) {
         FHS_CUDA(cudaFuncSetAttribute(keyswitch_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-        attr = true;
+        c->attr_ks = true;
     }
     const int n_tiles = (int)(((size_t)(c->n + 1) * 8 + kNT - 1) / kNT);
     const unsigned m_tiles = (unsigned)((batch + kMT - 1) / kMT);

@@ -15,3 +15,7 @@ timeout 600 $CMD > gpurun_out/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'blind_rotate|keyswitch' -s 6 -c 2 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
 tail -3 gpurun_out/ncu_full.log
+# wide (small-level) kernel: one capture at B=148
+timeout 300 python scratch/dev_br.py 148 > gpurun_out/plain_w.log 2>&1 &&
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:blind_rotate_wide -s 1 -c 1 -f -o gpurun_out/prof_wide python scratch/dev_br.py 148 > gpurun_out/ncu_wide.log 2>&1
+timeout 600 python bench_ops.py > gpurun_out/bench_ops.json 2> gpurun_out/bench_ops.err; cat gpurun_out/bench_ops.json
