@@ -20,6 +20,8 @@ struct SplitOps : StrOps {
     std::vector<Bool> non_overlapping(const std::vector<Bool> &m, const std::vector<Bool> &bz, bool reverse) {
         const size_t L1 = m.size();
         const size_t M = bz.size() - 1;  // max pattern length
+        serial_keep = M >= 2;
+        if (!serial_keep) return m;      // patterns of at most one char cannot overlap
         std::vector<Bool> chosen(L1);
         auto at = [&](size_t k) -> size_t { return reverse ? L1 - 1 - k : k; };
         for (size_t k = 0; k < L1; k++) {
@@ -36,7 +38,34 @@ struct SplitOps : StrOps {
         return chosen;
     }
 
+    // "value of the last set element" under the associative operator
+    //   (f1,v1) o (f2,v2) = (f1|f2, f2 ? v2 : v1),   invariant v = 0 whenever f = 0,
+    // so that f2 ? v2 : v1 = v2 + (f2 ? 0 : v1): one PBS per block and one for the flag, all in one level.
+    struct Last { Bool f; Rad v; };
+    Last last_combine(const Last &lo, const Last &hi) {
+        Last r;
+        r.f = bor(lo.f, hi.f);
+        Rad keep_lo = select_zero(bnot(hi.f), lo.v);
+        for (size_t b = 0; b < hi.v.size(); b++) r.v.push_back(bounded(add(hi.v[b], keep_lo[b]), 0, 3));
+        return r;
+    }
+    // inclusive prefix under last_combine: Brent-Kung (2 log2 n levels, < 2n combines) -- replaces the
+    // one-level-per-position chain of the reference's reverse loop (split.rs:274-319)
+    std::vector<Last> last_set_scan(const std::vector<Last> &x) {
+        const size_t n = x.size();
+        if (n <= 1) return x;
+        std::vector<Last> z(n / 2);
+        for (size_t k = 0; k < n / 2; k++) z[k] = last_combine(x[2 * k], x[2 * k + 1]);
+        std::vector<Last> w = last_set_scan(z);
+        std::vector<Last> y(n);
+        y[0] = x[0];
+        for (size_t k = 0; k < n / 2; k++) y[2 * k + 1] = w[k];
+        for (size_t k = 1; 2 * k < n; k++) y[2 * k] = last_combine(w[k - 1], x[2 * k]);
+        return y;
+    }
+
     enum Mode { SPLIT, INCLUSIVE, TERMINATOR };
+    bool serial_keep = false;   // set when the candidate selection below is a serial chain
 
     // Common engine.  `limit` (optional) = encrypted maximum number of pieces (splitn).
     FSliceVec split_engine(const FStr &a, const std::vector<Bool> &chosen, const Rad &plen, Mode mode,
@@ -56,12 +85,25 @@ struct SplitOps : StrOps {
                 cnt = inc_if(cnt, keep[i]);
             }
         }
-        // running piece start S_i (before position i)
+        // running piece start S_i (before position i) = i' + len(p) of the last kept match i' < i, else 0
         std::vector<Rad> S(L1 + 1);
         S[0] = usize(0);
-        for (size_t i = 0; i < L1; i++) {
-            Rad target = add_rad_scalar_len(plen, i);       // i + len(p)
-            S[i + 1] = if_then_else(keep[i], target, S[i]);
+        if (serial_keep || limit) {
+            // keep[] is itself a serial chain: the running start rides along, one level per position
+            for (size_t i = 0; i < L1; i++) {
+                Rad target = add_rad_scalar_len(plen, i);       // i + len(p)
+                S[i + 1] = if_then_else(keep[i], target, S[i]);
+            }
+        } else {
+            std::vector<Last> leaves(L1);
+            for (size_t i = 0; i < L1; i++)
+                leaves[i] = Last{keep[i], select_zero(keep[i], add_rad_scalar_len(plen, i))};
+            std::vector<Last> pre = last_set_scan(leaves);
+            for (size_t i = 0; i < L1; i++) {
+                S[i + 1] = pre[i].v;
+                for (auto &blk : S[i + 1])
+                    if (blk.noise > 24.f) blk = g.pbs(blk, [](int x) { return x & 3; }, 0, 3);
+            }
         }
         FSliceVec out;
         out.s = a;
@@ -117,6 +159,7 @@ struct SplitOps : StrOps {
         for (auto &c : a.ch) ws.push_back(is_whitespace(c));
         for (size_t i = 0; i < a.ch.size(); i++) ok.push_back(i == 0 ? Graph::constant(0) : bnot(ws[i - 1]));
         Rad one = usize(1);
+        serial_keep = false;
         return split_engine(a, ws, one, SPLIT, false, nullptr, &ok);
     }
     // split.rs:505/511
