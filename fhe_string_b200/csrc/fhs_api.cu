@@ -150,6 +150,12 @@ void fhs_ctx_destroy(fhs_ctx *h) {
     cudaFree(c->d_counter);
     for (int i = 0; i < 4; i++)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->copy_stream) {
+        cudaStreamSynchronize(c->copy_stream);
+        cudaStreamDestroy(c->copy_stream);
+        for (int i = 0; i < 7; i++)
+            if (c->ev_pipe[i]) cudaEventDestroy(c->ev_pipe[i]);
+    }
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -304,17 +310,65 @@ int fhs_ks_pbs_batch(fhs_ctx *h, const uint64_t *lwe_in, const uint32_t *lut_id,
     FHS_CUDA(cudaSetDevice(c->device));
     if ((rc = fhs::ensure_capacity(c, batch, n_luts)) != FHS_OK) return rc;
     const size_t w = (size_t)c->big + 1;
-    FHS_CUDA(cudaMemcpyAsync(c->d_in, lwe_in, batch * w * sizeof(uint64_t), cudaMemcpyHostToDevice,
-                             c->stream));
+    // Ciphertexts are independent, so the batch is cut at blind-rotation wave boundaries
+    // (4 ciphertexts per SM) into a short head, a body and the last partial wave: the body's
+    // upload and the head's download hide behind compute, only the head's upload and the tail's
+    // download stay exposed.  Batches of less than three waves go through in one piece.
+    const size_t wave = (size_t)4 * c->sm_count;
+    size_t cut[4] = {0, batch, batch, batch};
+    int n_chunks = 1;
+    if (batch >= 3 * wave) {
+        const size_t tail = batch % wave ? batch % wave : wave;
+        cut[1] = wave;
+        cut[2] = batch - tail;
+        cut[3] = batch;
+        n_chunks = 3;
+    }
     FHS_CUDA(cudaMemcpyAsync(c->d_lut_id, lut_id, batch * sizeof(uint32_t), cudaMemcpyHostToDevice,
                              c->stream));
     FHS_CUDA(cudaMemcpyAsync(c->d_tables, lut_tables, n_luts * c->space * sizeof(uint64_t),
                              cudaMemcpyHostToDevice, c->stream));
-    if ((rc = fhs_ks_pbs_batch_dev(h, c->d_in, c->d_lut_id, c->d_tables, n_luts, batch, c->d_out)) !=
-        FHS_OK)
-        return rc;
-    FHS_CUDA(cudaMemcpyAsync(lwe_out, c->d_out, batch * w * sizeof(uint64_t), cudaMemcpyDeviceToHost,
-                             c->stream));
+    if (n_chunks == 1) {
+        FHS_CUDA(cudaMemcpyAsync(c->d_in, lwe_in, batch * w * sizeof(uint64_t), cudaMemcpyHostToDevice,
+                                 c->stream));
+        if ((rc = fhs_ks_pbs_batch_dev(h, c->d_in, c->d_lut_id, c->d_tables, n_luts, batch, c->d_out)) !=
+            FHS_OK)
+            return rc;
+        FHS_CUDA(cudaMemcpyAsync(lwe_out, c->d_out, batch * w * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+                                 c->stream));
+        FHS_CUDA(cudaStreamSynchronize(c->stream));
+        return FHS_OK;
+    }
+    if (!c->copy_stream) {
+        FHS_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 7; i++) FHS_CUDA(cudaEventCreateWithFlags(&c->ev_pipe[i], cudaEventDisableTiming));
+    }
+    // the copy stream starts after whatever the compute stream still has queued on the staging buffers
+    FHS_CUDA(cudaEventRecord(c->ev_pipe[6], c->stream));
+    FHS_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_pipe[6], 0));
+    for (int i = 0; i < n_chunks; i++) {
+        const size_t lo = cut[i], nb = cut[i + 1] - cut[i];
+        FHS_CUDA(cudaMemcpyAsync(c->d_in + lo * w, lwe_in + lo * w, nb * w * sizeof(uint64_t),
+                                 cudaMemcpyHostToDevice, c->copy_stream));
+        FHS_CUDA(cudaEventRecord(c->ev_pipe[i], c->copy_stream));
+    }
+    FHS_CUDA(cudaEventRecord(c->ev[0], c->stream));
+    for (int i = 0; i < n_chunks; i++) {
+        const size_t lo = cut[i], nb = cut[i + 1] - cut[i];
+        FHS_CUDA(cudaStreamWaitEvent(c->stream, c->ev_pipe[i], 0));
+        uint64_t *small = c->d_small + lo * ((size_t)c->n + 1);
+        if ((rc = fhs::launch_keyswitch(c, c->d_in + lo * w, nb, small)) != FHS_OK) return rc;
+        if ((rc = fhs::launch_blind_rotate(c, small, c->d_lut_id + lo, c->d_tables, nb, c->d_out + lo * w)) !=
+            FHS_OK)
+            return rc;
+        FHS_CUDA(cudaEventRecord(c->ev_pipe[3 + i], c->stream));
+        FHS_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_pipe[3 + i], 0));
+        FHS_CUDA(cudaMemcpyAsync(lwe_out + lo * w, c->d_out + lo * w, nb * w * sizeof(uint64_t),
+                                 cudaMemcpyDeviceToHost, c->copy_stream));
+    }
+    FHS_CUDA(cudaEventRecord(c->ev[2], c->stream));
+    c->ev_valid[0] = c->ev_valid[1] = false;   // per-kernel split is not defined for interleaved chunks
+    FHS_CUDA(cudaStreamSynchronize(c->copy_stream));
     FHS_CUDA(cudaStreamSynchronize(c->stream));
     return FHS_OK;
 }

@@ -37,6 +37,8 @@ struct Ctx {
     uint64_t *d_tables = nullptr;
     size_t cap = 0, cap_tables = 0;
     unsigned int *d_counter = nullptr;
+    cudaStream_t copy_stream = nullptr;   // host-buffer calls: transfers overlapped with compute
+    cudaEvent_t ev_pipe[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     bool ev_valid[2] = {false, false};
     uint64_t launches = 0;

@@ -107,7 +107,9 @@ int fhs_pbs_batch_dev(fhs_ctx *ctx, const uint64_t *d_lwe_small_in, const uint32
                       uint64_t *d_lwe_out);
 
 /* Device-time of the most recent *_batch call's kernels in milliseconds (CUDA events on the
- * context's stream): [0]=keyswitch, [1]=blind rotation (+LUT build, sample extract). */
+ * context's stream): [0]=keyswitch, [1]=blind rotation (+LUT build, sample extract).  Both are 0
+ * after a host-buffer call that was pipelined (fhs_ks_pbs_batch with >= 12 ciphertexts per SM runs
+ * in three chunks whose transfers overlap the other chunks' kernels). */
 int fhs_last_kernel_ms(fhs_ctx *ctx, float *ms2);
 /* Number of kernels this context has launched so far. */
 uint64_t fhs_launch_count(fhs_ctx *ctx);
