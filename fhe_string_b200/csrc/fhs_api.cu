@@ -58,7 +58,8 @@ static void free_keys(Ctx *c) {
     cudaFree(c->d_ksk);
     cudaFree(c->d_ksk_corr);
     cudaFree(c->d_ksk_t);
-    c->d_ksk_t = nullptr;
+    cudaFree(c->d_ksk_u);
+    c->d_ksk_t = c->d_ksk_u = nullptr;
     cudaFree(c->d_bsk_f);
     cudaFree(c->d_bsk_w);
     c->d_ksk = c->d_ksk_corr = nullptr;
@@ -148,6 +149,7 @@ void fhs_ctx_destroy(fhs_ctx *h) {
     cudaFree(c->d_lut_id);
     cudaFree(c->d_tables);
     cudaFree(c->d_counter);
+    cudaFree(c->d_ks_digits);
     for (int i = 0; i < 4; i++)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->copy_stream) {
@@ -230,6 +232,7 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
         if ((e = cudaMalloc(&c->d_ksk, ksk_len * sizeof(uint64_t))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_ksk_corr, (c->n + 1) * sizeof(uint64_t))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_ksk_t, fhs::ksk_tiles_bytes(c))) != cudaSuccess ||
+            (e = cudaMalloc(&c->d_ksk_u, fhs::ksk_umma_tiles_bytes(c))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_bsk_f, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_bsk_w, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "cudaMalloc(keys)");
@@ -242,6 +245,7 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
         }
         if ((rc = fhs::launch_ksk_prepare(c, d_raw, ksk_level_order)) != FHS_OK) break;
         if ((rc = fhs::launch_ksk_tile(c)) != FHS_OK) break;
+        if ((rc = fhs::launch_ksk_tile_umma(c)) != FHS_OK) break;
         if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "ksk prepare");
             break;

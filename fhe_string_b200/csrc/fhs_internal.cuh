@@ -25,6 +25,9 @@ struct Ctx {
     // device key material
     uint64_t *d_ksk = nullptr;     // [k*N][ks_level (digit order, least significant first)][n+1]
     uint8_t *d_ksk_t = nullptr;    // byte-limb tiles of the KSK for the tensor-core keyswitch
+    uint8_t *d_ksk_u = nullptr;    // the same bytes as UMMA operand tiles (keyswitch_umma.cu)
+    uint8_t *d_ks_digits = nullptr;// scratch: signed digits of a batch as UMMA operand tiles
+    size_t cap_digits = 0;
     uint64_t *d_ksk_corr = nullptr;// [n+1]  2^(base_log-1) * sum of all KSK rows (unsigned-digit offset)
     double2 *d_bsk_f = nullptr;    // Fourier BSK, layout in blind_rotate.cu
     double2 *d_bsk_w = nullptr;    // the same values in the layout of blind_rotate_wide.cu
@@ -44,7 +47,7 @@ struct Ctx {
     uint64_t launches = 0;
     int sm_count = 0;
     // cudaFuncSetAttribute is per device: done once per context, not once per process
-    bool attr_br = false, attr_brw = false, attr_ks = false;
+    bool attr_br = false, attr_brw = false, attr_ks = false, attr_ksu = false;
 };
 
 void set_error(const char *fmt, ...);
@@ -63,6 +66,10 @@ int launch_ksk_prepare(Ctx *c, const uint64_t *d_ksk_raw, int level_order);
 size_t ksk_tiles_bytes(const Ctx *c);
 int launch_ksk_tile(Ctx *c);
 int launch_keyswitch_mma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_small);
+// keyswitch_umma.cu: tcgen05.mma kind::i8, accumulators in TMEM (large batches)
+size_t ksk_umma_tiles_bytes(const Ctx *c);
+int launch_ksk_tile_umma(Ctx *c);
+int launch_keyswitch_umma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_small);
 // blind_rotate.cu
 int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                         const uint64_t *d_tables, size_t batch, uint64_t *d_out);

@@ -31,14 +31,31 @@ def test_keyswitch_bit_exact(engine, keyset):
     assert np.array_equal(got, want)
 
 
-@pytest.mark.parametrize("batch", [1, 3, 29, 150, 600])
+@pytest.mark.parametrize("batch", [1, 3, 29, 150, 511, 512, 600, 1153])
 def test_keyswitch_tile_shapes(engine, keyset, batch):
+    """Every kernel behind fhs_keyswitch_batch (split-K mma.sync below 512 ciphertexts, tcgen05 from
+    512 up): rows are independent, so the oracle checks a sample that covers the tile boundaries."""
     rng = np.random.default_rng(batch)
     cts = rng.integers(0, 2**64, size=(batch, keyset.big), dtype=np.uint64)
     got = engine.keyswitch(cts)
-    idx = sorted(set([0, batch - 1, batch // 2]))
+    idx = sorted(set(i for i in [0, batch - 1, batch // 2, 127, 128, 255, 256, 511, 1023, 1024, 1152] if i < batch))
     want = keyset.keyswitch(cts[idx])
     assert np.array_equal(got[idx], want)
+
+
+def test_keyswitch_large_batch_edge_values(engine, keyset):
+    """Extreme mask values (all ones, sign bit, rounding ties) inside a batch that takes the tcgen05 path."""
+    rng = np.random.default_rng(77)
+    cts = rng.integers(0, 2**64, size=(640, keyset.big), dtype=np.uint64)
+    rows = [0, 127, 128, 300, 639]
+    cts[rows[0], :] = np.uint64(0xFFFFFFFFFFFFFFFF)
+    cts[rows[1], :] = np.uint64(0x8000000000000000)
+    cts[rows[2], :] = np.uint64(0x7FFFFFFFFFFFFFFF)
+    cts[rows[3], ::2] = np.uint64(0x0000FFFFFFFFFFFF)
+    cts[rows[4], :] = np.uint64(0x0001000000000000)      # exactly half of the last kept bit
+    got = engine.keyswitch(cts)
+    want = keyset.keyswitch(cts[rows])
+    assert np.array_equal(got[rows], want)
 
 
 def test_build_lut_bit_exact(engine, keyset):
