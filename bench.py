@@ -354,6 +354,12 @@ def main():
         achieved_tf = batch * FLOP_PER_PBS / (br_ms * 1e-3) / 1e12
         ks_bytes = 60_866_560 + batch * (16_392 + 5_944)
         ks_gbs = ks_bytes / (ks_ms * 1e-3) / 1e9 if ks_ms > 0 else None
+        # tensor-core view of the same kernel: [B x 10240] s8 digits x [10240 x 5944] u8 key bytes -> s32
+        ks_ops = 2.0 * batch * 10240 * 5944
+        ks_tops = ks_ops / (ks_ms * 1e-3) / 1e12 if ks_ms > 0 else None
+        i8_peak = 2.0 * float(peaks.get("bf16_tflops", 2250.0))
+        i8_src = ("2 x measured dense bf16 (MEASURED_PEAKS.json bf16_tflops, burst)" if "bf16_tflops" in peaks
+                  else "2 x nominal dense bf16 (B200_PROFILING.md fallback)")
         line = {
             "metric": METRIC, "value": value, "unit": "PBS/s", "n_gpus": world, "steps": args.steps,
             "warmup": warm, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
@@ -371,12 +377,15 @@ def main():
                          "peak_source": "measured in this run: DFMA chains (fhs_measure_fp64_tflops); "
                                         "MEASURED_PEAKS.json has no FP64 figure",
                          "algorithmic": f"{FLOP_PER_PBS} flop/PBS x {batch} PBS per launch"},
-            "roofline_keyswitch": {"bound": "hbm", "kernel": "keyswitch_kernel", "achieved": ks_gbs,
-                                   "peak": hbm_peak, "unit": "GB/s",
-                                   "frac": (ks_gbs / hbm_peak) if ks_gbs else None,
+            "roofline_keyswitch": {"bound": "tensor", "kernel": "ks_digits_kernel + keyswitch_umma_kernel",
+                                   "achieved": ks_tops, "peak": i8_peak, "unit": "TOP/s (int8)",
+                                   "frac": (ks_tops / i8_peak) if ks_tops else None,
                                    "traffic": traffic.get("keyswitch") if batch == BATCH else None,
-                                   "peak_source": hbm_src,
-                                   "algorithmic": f"{ks_bytes} B per launch (KSK once + B x (16392 + 5944))"},
+                                   "peak_source": i8_src,
+                                   "algorithmic": f"2 x {batch} x 10240 x 5944 int8 op per launch",
+                                   "hbm": {"achieved": ks_gbs, "peak": hbm_peak, "unit": "GB/s",
+                                           "frac": (ks_gbs / hbm_peak) if ks_gbs else None, "peak_source": hbm_src,
+                                           "algorithmic": f"{ks_bytes} B per launch (KSK once + B x (16392 + 5944))"}},
             "e2e": {"value": e2e_val, "unit": "PBS/s",
                     "h2d_bytes_per_step": int(batch * eng.big * 8 + batch * 4 + tables.size * 8) * world,
                     "d2h_bytes_per_step": int(batch * eng.big * 8) * world,

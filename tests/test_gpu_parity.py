@@ -33,8 +33,8 @@ def test_keyswitch_bit_exact(engine, keyset):
 
 @pytest.mark.parametrize("batch", [1, 3, 29, 150, 511, 512, 600, 1153])
 def test_keyswitch_tile_shapes(engine, keyset, batch):
-    """Every kernel behind fhs_keyswitch_batch (split-K mma.sync below 512 ciphertexts, tcgen05 from
-    512 up): rows are independent, so the oracle checks a sample that covers the tile boundaries."""
+    """fhs_keyswitch_batch (tcgen05 kernel, 128-ciphertext row tiles): rows are independent, so the
+    oracle checks a sample that covers the tile boundaries."""
     rng = np.random.default_rng(batch)
     cts = rng.integers(0, 2**64, size=(batch, keyset.big), dtype=np.uint64)
     got = engine.keyswitch(cts)
@@ -146,3 +146,34 @@ def test_noise_variance_1e5_samples(engine, keyset):
     assert var_gpu ** 0.5 < 3.2e-5
     assert abs(s1 / total) < 1e-6          # unbiased
     assert worst < 2.0 ** -9
+
+
+_VARIANT_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1])
+import fhe_string_b200 as F
+from oracle import oracle as O
+ks = O.Keyset(seed=1)
+eng = F.Engine(0)
+eng.upload_keys(ks.p, ks.ksk(), ks.bsk(), ksk_level_order=0)
+rng = np.random.default_rng(3)
+for batch in (5, 300):
+    cts = rng.integers(0, 2**64, size=(batch, ks.big), dtype=np.uint64)
+    got = eng.keyswitch(cts)
+    idx = [0, batch // 2, batch - 1]
+    assert np.array_equal(got[idx], ks.keyswitch(cts[idx])), batch
+print("variant ok")
+"""
+
+
+@pytest.mark.parametrize("variant", ["1", "2"])
+def test_keyswitch_baseline_kernels(variant):
+    """The IMAD (1) and mma.sync (2) keyswitch kernels stay in the library as A/B baselines of the
+    tcgen05 kernel; the variant is read once per process, hence the subprocess."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, FHS_KS_VARIANT=variant)
+    r = subprocess.run([sys.executable, "-c", _VARIANT_SCRIPT, root], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "variant ok" in r.stdout, r.stderr[-2000:]
