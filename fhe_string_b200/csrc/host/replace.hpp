@@ -63,12 +63,16 @@ struct ReplaceOps : SplitOps {
         std::vector<Bool> m = find_all(a, p, az, true);
         std::vector<Bool> chosen = non_overlapping(m, pz, false);
         if (n) {
+            // the first n matches are used: match i is used iff fewer than n matches precede it.  Counting
+            // ALL earlier matches (not the used ones) keeps the counter off the feedback path, so the
+            // increments ripple alongside the selection chain instead of adding ~7 levels per position.
             Rad cnt = usize(0);
+            std::vector<Bool> below(L1);
             for (size_t i = 0; i < L1; i++) {
-                Bool ok = Ops::lt(cnt, *n);
-                chosen[i] = band(chosen[i], ok);
+                below[i] = Ops::lt(cnt, *n);
                 cnt = inc_if(cnt, chosen[i]);
             }
+            for (size_t i = 0; i < L1; i++) chosen[i] = band(chosen[i], below[i]);
         }
         Rad slen = len_from_mask(sz);
         std::vector<Buf> nodes;

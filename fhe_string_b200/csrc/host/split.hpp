@@ -74,7 +74,8 @@ struct SplitOps : StrOps {
         Rad alen = len(a);
         std::vector<Bool> keep = chosen;
         if (limit) {
-            // a match is used only while fewer than limit-1 matches were used before it (scan order)
+            // a match is used iff fewer than limit-1 matches precede it in scan order.  The counter runs
+            // over ALL earlier matches, not the used ones (same predicate, no feedback through `keep`).
             Rad cnt = usize(0);
             Rad lim1 = sub_rad(*limit, usize(1));          // limit - 1 (limit == 0 handled below)
             Bool lim_zero = is_zero_rad(*limit);
@@ -82,14 +83,14 @@ struct SplitOps : StrOps {
                 size_t i = reverse_output ? L1 - 1 - k : k;
                 Bool ok = Ops::lt(cnt, lim1);
                 keep[i] = g.pbs(add(add(chosen[i], ok), bnot(lim_zero)), [](int x) { return x == 3; }, 0, 1);
-                cnt = inc_if(cnt, keep[i]);
+                cnt = inc_if(cnt, chosen[i]);
             }
         }
         // running piece start S_i (before position i) = i' + len(p) of the last kept match i' < i, else 0
         std::vector<Rad> S(L1 + 1);
         S[0] = usize(0);
-        if (serial_keep || limit) {
-            // keep[] is itself a serial chain: the running start rides along, one level per position
+        if (serial_keep && !reverse_output) {
+            // keep[] is itself a forward serial chain: the running start rides along, one level per position
             for (size_t i = 0; i < L1; i++) {
                 Rad target = add_rad_scalar_len(plen, i);       // i + len(p)
                 S[i + 1] = if_then_else(keep[i], target, S[i]);
