@@ -5,6 +5,7 @@
 // tests/split.rs:33-47), without special cases.  The greedy non-overlap decision is the only serial
 // part: one PBS of depth per position.
 #pragma once
+#include <functional>
 #include <map>
 
 #include "strings.hpp"
@@ -17,6 +18,30 @@ struct SplitOps : StrOps {
     // Greedy non-overlapping selection among candidate match starts m[i] for an encrypted pattern
     // b of at most M chars: chosen[i] = m[i] && no chosen match in the previous len(b)-1 positions
     // (forward) / next positions (reverse).  gp[d] = [len(b) > d] = [b[d] != 0].
+    //
+    // One scan step, with the earlier decisions supplied by `get` (k = index in scan order):
+    Bool overlap_step(const Bool &mk, size_t k, size_t M, const std::vector<Bool> &bz,
+                      const std::function<Bool(size_t)> &get) {
+        // far = sum_{d >= 2} chosen[k-d] & gp[d]   (at most one term is 1)
+        Lin far = Graph::constant(0);
+        for (size_t d = 2; d < M && d <= k; d++) {
+            Bool c = get(k - d);
+            if (c.is_const()) { if (c.c) far = add(far, bnot(bz[d])); continue; }
+            far = add(far, band(c, bnot(bz[d])));
+        }
+        far = bounded(far, 0, 1);
+        Lin near = Graph::constant(0);  // chosen[k-1] + gp[1]: busy iff == 2
+        if (k >= 1 && M >= 2) near = add(get(k - 1), bnot(bz[1]));
+        Lin x = add(add(scale(mk, 8), scale(far, 4)), near);
+        return g.pbs(x, [](int v) { return (v >> 3) == 1 && ((v >> 2) & 1) == 0 && (v & 3) < 2; }, 0, 1);
+    }
+    // The scan is a finite automaton whose state is the distance h to the nearest earlier chosen
+    // match (h < M matters, anything else = "none").  For M <= 8 the positions are cut into chunks of
+    // ~sqrt(2 L) and every chunk after the first is scanned for ALL M possible entry states at once
+    // (the hypothetical history is a plaintext constant); the true entry state of chunk j, a one-hot
+    // over h read off the resolved tail of chunk j-1, then selects among the M candidate results.
+    // Depth: chunk + 2 per chunk boundary instead of one level per position.
+    static constexpr size_t kSpecMaxPattern = 8;
     std::vector<Bool> non_overlapping(const std::vector<Bool> &m, const std::vector<Bool> &bz, bool reverse) {
         const size_t L1 = m.size();
         const size_t M = bz.size() - 1;  // max pattern length
@@ -24,17 +49,57 @@ struct SplitOps : StrOps {
         if (!serial_keep) return m;      // patterns of at most one char cannot overlap
         std::vector<Bool> chosen(L1);
         auto at = [&](size_t k) -> size_t { return reverse ? L1 - 1 - k : k; };
-        for (size_t k = 0; k < L1; k++) {
-            // far = sum_{d >= 2} chosen[k-d] & gp[d]   (at most one term is 1)
-            Lin far = Graph::constant(0);
-            for (size_t d = 2; d < M && d <= k; d++)
-                far = add(far, band(chosen[at(k - d)], bnot(bz[d])));
-            far = bounded(far, 0, 1);
-            Lin near = Graph::constant(0);  // chosen[k-1] + gp[1]: busy iff == 2
-            if (k >= 1 && M >= 2) near = add(chosen[at(k - 1)], bnot(bz[1]));
-            Lin x = add(add(scale(m[at(k)], 8), scale(far, 4)), near);
-            chosen[at(k)] = g.pbs(x, [](int v) { return (v >> 3) == 1 && ((v >> 2) & 1) == 0 && (v & 3) < 2; }, 0, 1);
+        size_t chunk = 1;
+        while (chunk * chunk < 2 * L1) chunk++;
+        if (chunk < M) chunk = M;
+        if (M > kSpecMaxPattern || L1 < 2 * chunk + 2) {
+            for (size_t k = 0; k < L1; k++)
+                chosen[at(k)] = overlap_step(m[at(k)], k, M, bz, [&](size_t kk) { return chosen[at(kk)]; });
+            return chosen;
         }
+        serial_keep = false;
+        std::vector<Bool> act(L1);       // resolved decisions, scan order
+        for (size_t k = 0; k < std::min(chunk, L1); k++)
+            act[k] = overlap_step(m[at(k)], k, M, bz, [&](size_t kk) { return act[kk]; });
+        // candidate results of every later chunk under every entry state
+        struct Cand { size_t p0, p1; std::vector<std::vector<Bool>> c; };   // c[h][k - p0]
+        std::vector<Cand> cands;
+        for (size_t p0 = chunk; p0 < L1; p0 += chunk) {
+            Cand cd{p0, std::min(L1, p0 + chunk), {}};
+            for (size_t h = 0; h < M; h++) {
+                std::vector<Bool> c(cd.p1 - p0);
+                for (size_t k = p0; k < cd.p1; k++)
+                    c[k - p0] = overlap_step(m[at(k)], k, M, bz, [&](size_t kk) -> Bool {
+                        if (kk >= p0) return c[kk - p0];
+                        return Graph::constant(h > 0 && kk + h == p0 ? 1 : 0);
+                    });
+                cd.c.push_back(c);
+            }
+            cands.push_back(cd);
+        }
+        for (auto &cd : cands) {
+            // entry state: hot[h] = act[p0-h] && none of act[p0-1 .. p0-h+1]; hot[0] = no chosen within M-1
+            std::vector<Bool> hot(M);
+            Lin seen = Graph::constant(0), any_hot = Graph::constant(0);
+            for (size_t h = 1; h < M; h++) {
+                const Bool &a = act[cd.p0 - h];
+                if (h == 1) hot[h] = a;
+                else hot[h] = g.pbs(sub(a, seen), [](int v) { return v == 1; }, 0, 1, true);
+                seen = add(seen, a);
+                any_hot = add(any_hot, hot[h]);
+            }
+            hot[0] = bounded(sub(Graph::constant(1), any_hot), 0, 1);
+            for (size_t k = cd.p0; k < cd.p1; k++) {
+                Lin v = Graph::constant(0);
+                for (size_t h = 0; h < M; h++) {
+                    const Bool &c = cd.c[h][k - cd.p0];
+                    if (c.is_const()) { if (c.c) v = add(v, hot[h]); continue; }
+                    v = add(v, band(hot[h], c));
+                }
+                act[k] = bounded(v, 0, 1);
+            }
+        }
+        for (size_t k = 0; k < L1; k++) chosen[at(k)] = act[k];
         return chosen;
     }
 

@@ -207,3 +207,39 @@ def test_slice_vector_len_and_get():
         for i in range(len(want) + 2):
             got = decode(gt.desc, eval_clear(ex, vals + usize_blocks(i)))
             assert got == (want[i] if i < len(want) else None), (s, pat, i, got)
+
+
+def _rust_rsplit(s, p):
+    """Rust rsplit: non-overlapping matches found right to left, pieces listed right to left."""
+    return s.rsplit(p)[::-1]
+
+
+LONG_OVERLAP = [("a" * 30, "aa", 33, None), ("a" * 31, "aaa", None, 5), ("ab" * 14 + "a", "aba", 32, None),
+                ("abcabcabcabcabcabcabcabcabcabc", "abcabc", None, 8), ("x" * 25 + "yx" * 4, "xx", 40, 4),
+                ("aabaabaabaabaabaabaabaab", "aabaa", None, None), ("b" * 24, "a", 30, 3)]
+
+
+@pytest.mark.parametrize("s,p,ps,pp", LONG_OVERLAP)
+def test_split_replace_long_overlapping(s, p, ps, pp):
+    """Strings long enough for the chunked (speculative) non-overlapping match selection and the
+    last-set scan of split.hpp, with matches that overlap in every possible phase."""
+    assert run("split", [s, p], [ps, pp]) == s.split(p)
+    assert run("rsplit", [s, p], [ps, pp]) == _rust_rsplit(s, p)
+    assert run("split_inclusive", [s, p], [ps, pp]) == rust_split_inclusive(s, p)
+    for n in (1, 2, 4, 30):
+        assert run("splitn", [s, p], [ps, pp], usizes=[n]) == s.split(p, n - 1)
+        assert run("rsplitn", [s, p], [ps, pp], usizes=[n]) == s.rsplit(p, n - 1)[::-1]
+    want = s.replace(p, "zz")
+    assert run("replace", [s, p, "zz"], [ps, pp, None], scalars=[len(want) + 1]) == want
+    wn = s.replace(p, "q", 3)
+    assert run("replacen", [s, p, "q"], [ps, pp, None], usizes=[3], scalars=[len(wn) + 1]) == wn
+
+
+def test_split_random_two_letter_alphabet():
+    rng = random.Random(5)
+    for _ in range(25):
+        s = "".join(rng.choice("ab") for _ in range(rng.randint(20, 34)))
+        p = "".join(rng.choice("ab") for _ in range(rng.randint(2, 4)))
+        pp = rng.choice([None, 5, 7])
+        assert run("split", [s, p], [36, pp]) == s.split(p)
+        assert run("rsplit", [s, p], [36, pp]) == _rust_rsplit(s, p)
