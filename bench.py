@@ -109,8 +109,8 @@ class ClockSampler:
 
 def string_op_latency(ck, eng):
     """BASELINE configs[2]: eq / contains / find (+ split) on a 64-char padded encrypted string with
-    an 8-char encrypted pattern; wall-clock per call through the public API (median of 3),
-    host<->device copies of the operand / result blocks included."""
+    an 8-char encrypted pattern; wall-clock per call through the public API (one warm-up call, then
+    the median of 5), host<->device copies of the operand / result blocks included."""
     from fhe_string_b200.api import ServerKey
     sk = ServerKey(ck, engine=eng)
     rng = np.random.default_rng(7)
@@ -121,7 +121,8 @@ def string_op_latency(ck, eng):
     for name, call, want in (("eq", lambda: es.eq(sk, es), True), ("contains", lambda: es.contains(sk, ep), True),
                              ("find", lambda: es.find(sk, ep), 13), ("split", lambda: es.split(sk, ep), s.split(pat))):
         ts = []
-        for _ in range(3):
+        call()
+        for _ in range(5):
             t0 = time.perf_counter()
             r = call()
             ts.append((time.perf_counter() - t0) * 1e3)
