@@ -243,3 +243,34 @@ def test_split_random_two_letter_alphabet():
         pp = rng.choice([None, 5, 7])
         assert run("split", [s, p], [36, pp]) == s.split(p)
         assert run("rsplit", [s, p], [36, pp]) == _rust_rsplit(s, p)
+
+
+def test_hypothesis_generated_ascii_strings():
+    """SURVEY 8(c) tier 1: hypothesis-generated ASCII inputs (small alphabet so that matches, overlaps
+    and repeated separators actually occur), every result against Python str semantics."""
+    from hypothesis import given, settings, strategies as st
+
+    alpha = st.sampled_from("ab ,")
+    text = st.text(alphabet=alpha, min_size=0, max_size=10)
+    pat = st.text(alphabet=alpha, min_size=0, max_size=3)
+
+    @settings(max_examples=60, deadline=None, derandomize=True)
+    @given(s=text, p=pat, ps=st.sampled_from([None, 12]), pp=st.sampled_from([None, 4]))
+    def check(s, p, ps, pp):
+        assert run("contains", [s, p], [ps, pp]) == (p in s)
+        f = s.find(p)
+        assert run("find", [s, p], [ps, pp]) == (None if f < 0 else f)
+        r = s.rfind(p)
+        assert run("rfind", [s, p], [ps, pp]) == (None if r < 0 else r)
+        assert run("lt", [s, p], [ps, pp]) == (s < p)
+        assert run("eq", [s, p], [ps, pp]) == (s == p)
+        assert run("trim", [s], [ps]) == s.strip(WS)
+        assert run("to_uppercase", [s], [ps]) == s.upper()
+        if p != "":
+            assert run("split", [s, p], [ps, pp]) == s.split(p)
+            assert run("rsplit", [s, p], [ps, pp]) == s.rsplit(p)[::-1]
+            want = s.replace(p, "xy")
+            assert run("replace", [s, p, "xy"], [ps, pp, None], scalars=[len(want) + 1]) == want
+        assert run("split_ascii_whitespace", [s], [ps]) == s.split()
+
+    check()

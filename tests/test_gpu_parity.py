@@ -80,6 +80,18 @@ def test_ks_pbs_decrypts_and_noise(engine, keyset):
     assert np.abs(err).max() < 2.0**-9  # half a box is 2^-6
 
 
+@pytest.mark.parametrize("n", [1776, 1777, 2500])
+def test_ks_pbs_pipelined_host_call(engine, keyset, n):
+    """fhs_ks_pbs_batch cuts batches of >= 3 blind-rotation waves (3 x 592) into head / body / tail
+    chunks whose transfers overlap the other chunks' kernels: every block must come back with its own
+    LUT applied (chunk offsets of lut_id, inputs and outputs), pageable host memory included."""
+    tables = bench_tables()
+    msgs, cts = _mixed_inputs(keyset, n, 4000 + n)
+    lut_id = ((np.arange(n) * 5 + 3) % 8).astype(np.uint32)
+    out = engine.ks_pbs(cts, lut_id, tables)
+    assert np.array_equal(keyset.decrypt(out), tables[lut_id, msgs])
+
+
 def test_blind_rotate_close_to_oracle(engine, keyset):
     """Same small-key LWE in, GPU vs oracle blind rotation: identical up to FFT rounding noise."""
     tables = bench_tables()
