@@ -67,26 +67,47 @@ __device__ __forceinline__ void w_ldg_b128(const void *p, uint32_t &a, uint32_t 
 }
 __device__ __forceinline__ double w_dbl(uint32_t lo, uint32_t hi) { return __hiloint2double((int)hi, (int)lo); }
 
-// x[slot] *= (tx + i ty) or its conjugate, twiddles read 4 at a time from 16 TMEM columns
-template <bool kConj, int kPerm>
-__device__ __forceinline__ void w_twiddle16(double (&xr)[16], double (&xi)[16], uint32_t tcol) {
+// tcgen05.wait::ld with the loaded registers as read-write operands: later uses cannot be scheduled
+// above the wait, and the registers stay reserved while the asynchronous load is in flight.
+__device__ __forceinline__ void w_wait_ld16(uint32_t (&r)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :: "memory");
+}
+
+template <bool kConj, int kPerm, int kChunk>
+__device__ __forceinline__ void w_twiddle4(double (&xr)[16], double (&xi)[16], const uint32_t (&tw)[16]) {
 #pragma unroll
-    for (int c = 0; c < 4; c++) {
-        uint32_t tw[16];
-        tmem_ld16(tcol + 16 * c, tw);
-        tmem_wait_ld();
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int n = 4 * c + k;
-            // kPerm 0: natural slot; 4: slot BR4(n); 3: slot 8*(n>>3) + BR3(n&7)
-            const int s = kPerm == 4 ? FHS_BR4(n) : (kPerm == 3 ? ((n & 8) | FHS_BR3(n & 7)) : n);
-            const double tx = w_dbl(tw[4 * k + 0], tw[4 * k + 1]);
-            const double ty = kConj ? -w_dbl(tw[4 * k + 2], tw[4 * k + 3]) : w_dbl(tw[4 * k + 2], tw[4 * k + 3]);
-            const double a = xr[s], b = xi[s];
-            xr[s] = a * tx - b * ty;
-            xi[s] = a * ty + b * tx;
-        }
+    for (int k = 0; k < 4; k++) {
+        const int n = 4 * kChunk + k;
+        // kPerm 0: natural slot; 4: slot BR4(n); 3: slot 8*(n>>3) + BR3(n&7)
+        const int s = kPerm == 4 ? FHS_BR4(n) : (kPerm == 3 ? ((n & 8) | FHS_BR3(n & 7)) : n);
+        const double tx = w_dbl(tw[4 * k + 0], tw[4 * k + 1]);
+        const double ty = kConj ? -w_dbl(tw[4 * k + 2], tw[4 * k + 3]) : w_dbl(tw[4 * k + 2], tw[4 * k + 3]);
+        const double a = xr[s], b = xi[s];
+        xr[s] = a * tx - b * ty;
+        xi[s] = a * ty + b * tx;
     }
+}
+// x[slot] *= (tx + i ty) or its conjugate, twiddles 4 at a time from 16 TMEM columns.  The caller has
+// already requested chunk 0 into `tw0` (before the codelet that precedes the multiplication), and each
+// further chunk is requested before the previous one is consumed, so the TMEM round trips overlap the
+// arithmetic instead of serialising with it.
+template <bool kConj, int kPerm>
+__device__ __forceinline__ void w_twiddle16(double (&xr)[16], double (&xi)[16], uint32_t tcol, uint32_t (&tw0)[16]) {
+    uint32_t tw1[16];
+    w_wait_ld16(tw0);
+    tmem_ld16(tcol + 16, tw1);
+    w_twiddle4<kConj, kPerm, 0>(xr, xi, tw0);
+    w_wait_ld16(tw1);
+    tmem_ld16(tcol + 32, tw0);
+    w_twiddle4<kConj, kPerm, 1>(xr, xi, tw1);
+    w_wait_ld16(tw0);
+    tmem_ld16(tcol + 48, tw1);
+    w_twiddle4<kConj, kPerm, 2>(xr, xi, tw0);
+    w_wait_ld16(tw1);
+    w_twiddle4<kConj, kPerm, 3>(xr, xi, tw1);
 }
 
 __global__ void __launch_bounds__(kWThreads, 1)
@@ -230,8 +251,10 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                     }
                 }
                 // ---- forward pass 1, twiddle 1, exchange 1 ----
+                uint32_t twp[16];
+                tmem_ld16(ttw1, twp);
                 fft16_pos(xr, xi);
-                w_twiddle16<false, 0>(xr, xi, ttw1);
+                w_twiddle16<false, 0>(xr, xi, ttw1, twp);
 #pragma unroll
                 for (int k1 = 0; k1 < 16; k1++) E1[k1 * kE1Stride + t] = make_double2(xr[k1], xi[k1]);
                 wbar_sync(bar_poly, 64);
@@ -243,9 +266,10 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                     xi[8 * e + FHS_BR3(j2)] = val.y;
                 }
                 // ---- forward pass 2, twiddle 2, exchange 2 ----
+                tmem_ld16(ttw2, twp);
                 fft8_pos_lo(xr, xi);
                 fft8_pos_hi(xr, xi);
-                w_twiddle16<false, 0>(xr, xi, ttw2);
+                w_twiddle16<false, 0>(xr, xi, ttw2, twp);
 #pragma unroll
                 for (int n = 0; n < 16; n++) {
                     const int e = n >> 3, k2 = n & 7;
@@ -265,25 +289,34 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                 // ---- GGSW contraction against the BSK slice parked in TMEM ----
                 wbar_sync(kWBarFull, bar_threads);
                 tmem_fence_after_sync();
+                {
+                    uint32_t br0[16], br1[16];
+                    auto contract2 = [&](const uint32_t (&br)[16], int f0) {
 #pragma unroll
-                for (int b = 0; b < 4; b++) {
-                    uint32_t br[32];
-                    tmem_ld32(tbsk + 32 * b, br);
-                    tmem_wait_ld();
+                        for (int k = 0; k < 2; k++) {
+                            const int f = f0 + k;
+                            const double csx = w_dbl(br[8 * k + 0], br[8 * k + 1]);
+                            const double csy = w_dbl(br[8 * k + 2], br[8 * k + 3]);
+                            const double ckx = w_dbl(br[8 * k + 4], br[8 * k + 5]);
+                            const double cky = w_dbl(br[8 * k + 6], br[8 * k + 7]);
+                            const double dr = xr[f], di = xi[f];
+                            const double sr = dr * csx - di * csy;
+                            const double si = dr * csy + di * csx;
+                            const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
+                            const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
+                            xr[f] = fma(dr, ckx, fma(-di, cky, gr));
+                            xi[f] = fma(dr, cky, fma(di, ckx, gi));
+                        }
+                    };
+                    tmem_ld16(tbsk, br0);
 #pragma unroll
-                    for (int k = 0; k < 4; k++) {
-                        const int f = 4 * b + k;
-                        const double csx = w_dbl(br[8 * k + 0], br[8 * k + 1]);
-                        const double csy = w_dbl(br[8 * k + 2], br[8 * k + 3]);
-                        const double ckx = w_dbl(br[8 * k + 4], br[8 * k + 5]);
-                        const double cky = w_dbl(br[8 * k + 6], br[8 * k + 7]);
-                        const double dr = xr[f], di = xi[f];
-                        const double sr = dr * csx - di * csy;
-                        const double si = dr * csy + di * csx;
-                        const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
-                        const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
-                        xr[f] = fma(dr, ckx, fma(-di, cky, gr));
-                        xi[f] = fma(dr, cky, fma(di, ckx, gi));
+                    for (int b = 0; b < 8; b += 2) {
+                        w_wait_ld16(br0);
+                        tmem_ld16(tbsk + 16 * (b + 1), br1);
+                        contract2(br0, 2 * b);
+                        w_wait_ld16(br1);
+                        if (b + 2 < 8) tmem_ld16(tbsk + 16 * (b + 2), br0);
+                        contract2(br1, 2 * b + 2);
                     }
                 }
                 if (!(g == last_group && i == n_lwe - 1)) {
@@ -308,6 +341,7 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                     E2r[(q + 64 * e) * kE2Stride + j3] = make_double2(xr[n], xi[n]);
                 }
                 wbar_sync(bar_ct, 128);
+                tmem_ld16(ttw2, twp);
 #pragma unroll
                 for (int n = 0; n < 16; n++) {
                     const int e = n >> 3, k2 = n & 7;
@@ -316,7 +350,7 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                     xi[8 * e + FHS_BR3(k2)] = val.y;
                 }
                 // ---- conjugate twiddle 2, inverse pass 2, exchange 1 back ----
-                w_twiddle16<true, 3>(xr, xi, ttw2);
+                w_twiddle16<true, 3>(xr, xi, ttw2, twp);
                 fft8_neg_lo(xr, xi);
                 fft8_neg_hi(xr, xi);
 #pragma unroll
@@ -325,6 +359,7 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                     E1[k1u * kE1Stride + 8 * j2 + j3u + 4 * e] = make_double2(xr[n], xi[n]);
                 }
                 wbar_sync(bar_poly, 64);
+                tmem_ld16(ttw1, twp);
 #pragma unroll
                 for (int k1 = 0; k1 < 16; k1++) {
                     const double2 val = E1[k1 * kE1Stride + t];
@@ -332,7 +367,7 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                     xi[FHS_BR4(k1)] = val.y;
                 }
                 // ---- conjugate twiddle 1, inverse pass 1 ----
-                w_twiddle16<true, 4>(xr, xi, ttw1);
+                w_twiddle16<true, 4>(xr, xi, ttw1, twp);
                 fft16_neg(xr, xi);
                 // ---- conjugate pre-twist, add as torus into the TMEM accumulator + hi plane ----
                 {
