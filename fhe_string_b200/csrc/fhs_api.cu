@@ -118,6 +118,12 @@ int fhs_ctx_create(int device, fhs_ctx **out) {
     }
     FHS_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
+    {   // ciphertext pools use the stream-ordered allocator (level.cu): keep freed blocks cached
+        cudaMemPool_t mp;
+        FHS_CUDA(cudaDeviceGetDefaultMemPool(&mp, device));
+        uint64_t keep = ~0ull;
+        FHS_CUDA(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     for (int i = 0; i < 4; i++) FHS_CUDA(cudaEventCreate(&c->ev[i]));
     FHS_CUDA(cudaMalloc(&c->d_counter, 64));
     // inter-pass twiddles T[k2][n1] = e^{2 pi i n1 (k2 + 1/4)/1024}, padded rows of 33

@@ -45,34 +45,44 @@ gather_linear_kernel(const uint64_t *__restrict__ pool, const uint32_t *__restri
     }
 }
 
+// Pool memory comes from the device's stream-ordered allocator on the context's stream (the default
+// mempool keeps freed blocks cached: fhs_ctx_create lifts its release threshold), so creating and
+// destroying a pool per operation costs microseconds instead of a cudaMalloc / cudaFree round trip each.
+template <class T> cudaError_t pool_alloc(Ctx *c, T **p, size_t bytes) {
+    return cudaMallocAsync(reinterpret_cast<void **>(p), bytes, c->stream);
+}
+inline void pool_free(Ctx *c, void *p) {
+    if (p) cudaFreeAsync(p, c->stream);
+}
+
 int ensure_desc(Pool *p, size_t B, size_t T, size_t n_luts) {
     Ctx *c = p->ctx;
     if (B > p->cap_b) {
         size_t cap = p->cap_b ? p->cap_b : 1024;
         while (cap < B) cap *= 2;
-        cudaFree(p->d_off); cudaFree(p->d_lut); cudaFree(p->d_cst); cudaFree(p->d_stage);
+        pool_free(c, p->d_off); pool_free(c, p->d_lut); pool_free(c, p->d_cst); pool_free(c, p->d_stage);
         p->d_off = p->d_lut = nullptr; p->d_cst = nullptr; p->d_stage = nullptr; p->cap_b = 0;
-        FHS_CUDA(cudaMalloc(&p->d_off, (cap + 1) * sizeof(uint32_t)));
-        FHS_CUDA(cudaMalloc(&p->d_lut, cap * sizeof(uint32_t)));
-        FHS_CUDA(cudaMalloc(&p->d_cst, cap * sizeof(uint64_t)));
-        FHS_CUDA(cudaMalloc(&p->d_stage, cap * ((size_t)c->big + 1) * sizeof(uint64_t)));
+        FHS_CUDA(fhs::pool_alloc(c, &p->d_off, (cap + 1) * sizeof(uint32_t)));
+        FHS_CUDA(fhs::pool_alloc(c, &p->d_lut, cap * sizeof(uint32_t)));
+        FHS_CUDA(fhs::pool_alloc(c, &p->d_cst, cap * sizeof(uint64_t)));
+        FHS_CUDA(fhs::pool_alloc(c, &p->d_stage, cap * ((size_t)c->big + 1) * sizeof(uint64_t)));
         p->cap_b = cap;
     }
     if (T > p->cap_t) {
         size_t cap = p->cap_t ? p->cap_t : 4096;
         while (cap < T) cap *= 2;
-        cudaFree(p->d_idx); cudaFree(p->d_coef);
+        pool_free(c, p->d_idx); pool_free(c, p->d_coef);
         p->d_idx = nullptr; p->d_coef = nullptr; p->cap_t = 0;
-        FHS_CUDA(cudaMalloc(&p->d_idx, cap * sizeof(uint32_t)));
-        FHS_CUDA(cudaMalloc(&p->d_coef, cap * sizeof(int32_t)));
+        FHS_CUDA(fhs::pool_alloc(c, &p->d_idx, cap * sizeof(uint32_t)));
+        FHS_CUDA(fhs::pool_alloc(c, &p->d_coef, cap * sizeof(int32_t)));
         p->cap_t = cap;
     }
     if (n_luts > p->cap_luts) {
         size_t cap = p->cap_luts ? p->cap_luts : 64;
         while (cap < n_luts) cap *= 2;
-        cudaFree(p->d_tables);
+        pool_free(c, p->d_tables);
         p->d_tables = nullptr; p->cap_luts = 0;
-        FHS_CUDA(cudaMalloc(&p->d_tables, cap * c->space * sizeof(uint64_t)));
+        FHS_CUDA(fhs::pool_alloc(c, &p->d_tables, cap * c->space * sizeof(uint64_t)));
         p->cap_luts = cap;
     }
     return FHS_OK;
@@ -93,8 +103,10 @@ int fhs_pool_create(fhs_ctx *h, size_t capacity_blocks, fhs_pool **out) {
     FHS_CUDA(cudaSetDevice(c->device));
     Pool *p = new Pool();
     p->ctx = c;
-    cudaError_t e = cudaMalloc(&p->d, capacity_blocks * ((size_t)c->big + 1) * sizeof(uint64_t));
-    if (e != cudaSuccess) { delete p; return fhs::cuda_fail(e, "cudaMalloc(pool)"); }
+    cudaError_t e = fhs::pool_alloc(c, &p->d, capacity_blocks * ((size_t)c->big + 1) * sizeof(uint64_t));
+    if (e != cudaSuccess) { delete p; return fhs::cuda_fail(e, "cudaMallocAsync(pool)"); }
+    // other streams (the pool's copy stream, a caller's NCCL stream) may touch the block right away
+    if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) { delete p; return fhs::cuda_fail(e, "pool alloc sync"); }
     p->capacity = capacity_blocks;
     *out = reinterpret_cast<fhs_pool *>(p);
     return FHS_OK;
@@ -104,12 +116,12 @@ void fhs_pool_destroy(fhs_pool *hp) {
     Pool *p = reinterpret_cast<Pool *>(hp);
     if (!p) return;
     cudaSetDevice(p->ctx->device);
-    cudaStreamSynchronize(p->ctx->stream);
-    cudaFree(p->d); cudaFree(p->d_off); cudaFree(p->d_idx); cudaFree(p->d_lut); cudaFree(p->d_coef);
-    cudaFree(p->d_cst); cudaFree(p->d_tables); cudaFree(p->d_stage);
-    cudaFree(p->r_off); cudaFree(p->r_idx); cudaFree(p->r_lut); cudaFree(p->r_coef);
-    cudaFree(p->r_cst); cudaFree(p->r_tables); cudaFree(p->r_stage);
+    Ctx *c = p->ctx;
+    cudaStreamSynchronize(c->stream);
     if (p->copy_stream) { cudaStreamSynchronize(p->copy_stream); cudaStreamDestroy(p->copy_stream); }
+    void *all[] = {p->d, p->d_off, p->d_idx, p->d_lut, p->d_coef, p->d_cst, p->d_tables, p->d_stage,
+                   p->r_off, p->r_idx, p->r_lut, p->r_coef, p->r_cst, p->r_tables, p->r_stage};
+    for (void *q : all) fhs::pool_free(c, q);
     if (p->write_done) cudaEventDestroy(p->write_done);
     delete p;
 }
@@ -223,19 +235,21 @@ int fhs_pool_load_program(fhs_pool *hp, size_t rows, size_t terms, const uint32_
     FHS_CUDA(cudaSetDevice(c->device));
     cudaStream_t s = c->stream;
     FHS_CUDA(cudaStreamSynchronize(s));
-    cudaFree(p->r_off); cudaFree(p->r_idx); cudaFree(p->r_lut); cudaFree(p->r_coef);
-    cudaFree(p->r_cst); cudaFree(p->r_tables); cudaFree(p->r_stage);
+    {
+        void *old[] = {p->r_off, p->r_idx, p->r_lut, p->r_coef, p->r_cst, p->r_tables, p->r_stage};
+        for (void *q : old) fhs::pool_free(c, q);
+    }
     p->r_off = p->r_idx = p->r_lut = nullptr; p->r_coef = nullptr;
     p->r_cst = p->r_tables = p->r_stage = nullptr;
     p->r_rows = 0;
     const size_t w = (size_t)c->big + 1;
-    FHS_CUDA(cudaMalloc(&p->r_off, (rows + 1) * sizeof(uint32_t)));
-    FHS_CUDA(cudaMalloc(&p->r_idx, (terms + 1) * sizeof(uint32_t)));
-    FHS_CUDA(cudaMalloc(&p->r_coef, (terms + 1) * sizeof(int32_t)));
-    FHS_CUDA(cudaMalloc(&p->r_cst, (rows + 1) * sizeof(uint64_t)));
-    FHS_CUDA(cudaMalloc(&p->r_lut, (rows + 1) * sizeof(uint32_t)));
-    FHS_CUDA(cudaMalloc(&p->r_tables, (n_luts + 1) * c->space * sizeof(uint64_t)));
-    FHS_CUDA(cudaMalloc(&p->r_stage, (max_level_rows + 1) * w * sizeof(uint64_t)));
+    FHS_CUDA(fhs::pool_alloc(c, &p->r_off, (rows + 1) * sizeof(uint32_t)));
+    FHS_CUDA(fhs::pool_alloc(c, &p->r_idx, (terms + 1) * sizeof(uint32_t)));
+    FHS_CUDA(fhs::pool_alloc(c, &p->r_coef, (terms + 1) * sizeof(int32_t)));
+    FHS_CUDA(fhs::pool_alloc(c, &p->r_cst, (rows + 1) * sizeof(uint64_t)));
+    FHS_CUDA(fhs::pool_alloc(c, &p->r_lut, (rows + 1) * sizeof(uint32_t)));
+    FHS_CUDA(fhs::pool_alloc(c, &p->r_tables, (n_luts + 1) * c->space * sizeof(uint64_t)));
+    FHS_CUDA(fhs::pool_alloc(c, &p->r_stage, (max_level_rows + 1) * w * sizeof(uint64_t)));
     FHS_CUDA(cudaMemcpyAsync(p->r_off, row_off, (rows + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
     if (terms) {
         FHS_CUDA(cudaMemcpyAsync(p->r_idx, term_idx, terms * sizeof(uint32_t), cudaMemcpyHostToDevice, s));
