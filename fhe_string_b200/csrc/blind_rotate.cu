@@ -173,7 +173,53 @@ __device__ __forceinline__ void ldg_b128(const void *p, uint32_t &a, uint32_t &b
                  : "l"(p));
 }
 
-// kOpt bit 2: rotated gather of the hi plane with one LOP3 per address (8 KB aligned planes) and the
+// tcgen05.wait::ld carrying the loaded registers as read-write operands (uses cannot move above it)
+__device__ __forceinline__ void wait_ld_dep16(uint32_t (&r)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :: "memory");
+}
+__device__ __forceinline__ void wait_ld_dep32(uint32_t (&r)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                   "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                   "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :: "memory");
+}
+// one 32-column chunk of the BSK slice = 4 frequencies: 2x2 GGSW contraction with one shfl_xor(16)
+__device__ __forceinline__ void contract4(double (&xr)[32], double (&xi)[32], const uint32_t (&br)[32], int k0) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int k1 = k0 + k;
+        const double csx = __hiloint2double((int)br[8 * k + 1], (int)br[8 * k + 0]);
+        const double csy = __hiloint2double((int)br[8 * k + 3], (int)br[8 * k + 2]);
+        const double ckx = __hiloint2double((int)br[8 * k + 5], (int)br[8 * k + 4]);
+        const double cky = __hiloint2double((int)br[8 * k + 7], (int)br[8 * k + 6]);
+        const double dr = xr[k1], di = xi[k1];
+        const double sr = dr * csx - di * csy;
+        const double si = dr * csy + di * csx;
+        const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
+        const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
+        xr[k1] = fma(dr, ckx, fma(-di, cky, gr));
+        xi[k1] = fma(dr, cky, fma(di, ckx, gi));
+    }
+}
+__device__ __forceinline__ void inv_twiddle4(double (&xr)[32], double (&xi)[32], const uint32_t (&tw)[16], int n0) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int n1 = n0 + k;
+        const double tx = __hiloint2double((int)tw[4 * k + 1], (int)tw[4 * k + 0]);
+        const double ty = __hiloint2double((int)tw[4 * k + 3], (int)tw[4 * k + 2]);
+        const double a0 = xr[n1], b0 = xi[n1];
+        xr[n1] = a0 * tx + b0 * ty;
+        xi[n1] = b0 * tx - a0 * ty;
+    }
+}
+
+// kOpt bit 2: rotated gather of the hi plane
+// kOpt bit 3: TMEM loads (BSK slice, inverse twiddles) are requested one chunk ahead of their use. with one LOP3 per address (8 KB aligned planes) and the
 // negacyclic sign taken from a pre-shifted offset (-160 integer instructions per CMUX).
 // kOpt bit 0: inverse twiddles (the row T[rk2][0..31] every thread multiplies by after the inverse
 // row pass) live in the 128 TMEM columns the accumulator and the BSK slice leave free, instead of
@@ -315,44 +361,51 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 double xr[32], xi[32];
                 // ---- (X^a - 1) * acc_w on high words, signed digit, pre-twist ----
                 {
-                    uint32_t own[64];
-                    tmem_ld64(tacc, own);
+                    uint32_t own_l[64];
+                    tmem_ld64(tacc, own_l);
                     const uint32_t base = (uint32_t)(lane - (int)a) & (2 * kN - 1);
                     // byte offset of coefficient (lane - a) mod 2N, pre-shifted so that the
                     // negacyclic sign (bit 13) is the top bit: + (m << 25) walks the 32 rows mod 2^32
                     const uint32_t off_s = base << 20;
                     tmem_wait_ld();
+                    auto digits8 = [&](const uint32_t *own, int m0) {
 #pragma unroll
-                    for (int m = 0; m < 32; m++) {
-                        uint32_t r0, r1;
-                        if (kOpt & 4) {
-                            const uint32_t t0 = off_s + ((uint32_t)m << 25);     // idx0 << 20
-                            const uint32_t t1 = t0 + (1u << 30);                // (idx0 + N/2) << 20
-                            const uint32_t a0 = h_plane | ((t0 >> 18) & 0x1FFCu);
-                            const uint32_t a1 = a0 ^ 0x1000u;
-                            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r0) : "r"(a0) : "memory");
-                            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r1) : "r"(a1) : "memory");
-                            r0 ^= (uint32_t)((int)t0 >> 31);
-                            r1 ^= (uint32_t)((int)t1 >> 31);
-                        } else {
-                            const uint32_t idx0 = (base + 32 * m) & (2 * kN - 1);
-                            const uint32_t idx1 = (idx0 + kH) & (2 * kN - 1);
-                            r0 = H[idx0 & (kN - 1)];
-                            r1 = H[idx1 & (kN - 1)];
-                            // negacyclic wrap: -x on the high word is ~x up to the dropped borrow
-                            r0 ^= (uint32_t)((int)(idx0 << 20) >> 31);
-                            r1 ^= (uint32_t)((int)(idx1 << 20) >> 31);
+                        for (int mm = 0; mm < 8; mm++) {
+                            const int m = m0 + mm;
+                            uint32_t r0, r1;
+                            if (kOpt & 4) {
+                                const uint32_t t0 = off_s + ((uint32_t)m << 25);     // idx0 << 20
+                                const uint32_t t1 = t0 + (1u << 30);                // (idx0 + N/2) << 20
+                                const uint32_t a0 = h_plane | ((t0 >> 18) & 0x1FFCu);
+                                const uint32_t a1 = a0 ^ 0x1000u;
+                                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r0) : "r"(a0) : "memory");
+                                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r1) : "r"(a1) : "memory");
+                                r0 ^= (uint32_t)((int)t0 >> 31);
+                                r1 ^= (uint32_t)((int)t1 >> 31);
+                            } else {
+                                const uint32_t idx0 = (base + 32 * m) & (2 * kN - 1);
+                                const uint32_t idx1 = (idx0 + kH) & (2 * kN - 1);
+                                r0 = H[idx0 & (kN - 1)];
+                                r1 = H[idx1 & (kN - 1)];
+                                // negacyclic wrap: -x on the high word is ~x up to the dropped borrow
+                                r0 ^= (uint32_t)((int)(idx0 << 20) >> 31);
+                                r1 ^= (uint32_t)((int)(idx1 << 20) >> 31);
+                            }
+                            const double d0 = __int2double_rn(pbs_digit_hi(r0 - own[2 * mm]));
+                            const double d1 = __int2double_rn(pbs_digit_hi(r1 - own[2 * mm + 1]));
+                            if (m == 0) {
+                                xr[FHS_BR5(m)] = d0;
+                                xi[FHS_BR5(m)] = d1;
+                            } else {
+                                xr[FHS_BR5(m)] = d0 * fhs_pre_re(m) - d1 * fhs_pre_im(m);
+                                xi[FHS_BR5(m)] = d0 * fhs_pre_im(m) + d1 * fhs_pre_re(m);
+                            }
                         }
-                        const double d0 = __int2double_rn(pbs_digit_hi(r0 - own[2 * m]));
-                        const double d1 = __int2double_rn(pbs_digit_hi(r1 - own[2 * m + 1]));
-                        if (m == 0) {
-                            xr[FHS_BR5(m)] = d0;
-                            xi[FHS_BR5(m)] = d1;
-                        } else {
-                            xr[FHS_BR5(m)] = d0 * fhs_pre_re(m) - d1 * fhs_pre_im(m);
-                            xi[FHS_BR5(m)] = d0 * fhs_pre_im(m) + d1 * fhs_pre_re(m);
-                        }
-                    }
+                    };
+                    digits8(own_l, 0);
+                    digits8(own_l + 16, 8);
+                    digits8(own_l + 32, 16);
+                    digits8(own_l + 48, 24);
                 }
                 fwd_cols(xr, xi, sm.T, lane);
                 if (stag) named_bar_sync(tok_wait, 256);
@@ -377,25 +430,39 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                 // ---- GGSW contraction against the BSK slice parked in TMEM ----
                 named_bar_sync(bar_full, bar_threads);
                 tmem_fence_after_sync();
+                if (kOpt & 8) {
+                    uint32_t br0[32], br1[32];
+                    tmem_ld32(tbsk, br0);
 #pragma unroll
-                for (int b = 0; b < 8; b++) {
-                    uint32_t br[32];
-                    tmem_ld32(tbsk + 32 * b, br);
-                    tmem_wait_ld();
+                    for (int b = 0; b < 8; b += 2) {
+                        wait_ld_dep32(br0);
+                        tmem_ld32(tbsk + 32 * (b + 1), br1);
+                        contract4(xr, xi, br0, 4 * b);
+                        wait_ld_dep32(br1);
+                        if (b + 2 < 8) tmem_ld32(tbsk + 32 * (b + 2), br0);
+                        contract4(xr, xi, br1, 4 * b + 4);
+                    }
+                } else {
 #pragma unroll
-                    for (int k = 0; k < 4; k++) {
-                        const int k1 = 4 * b + k;
-                        const double csx = __hiloint2double((int)br[8 * k + 1], (int)br[8 * k + 0]);
-                        const double csy = __hiloint2double((int)br[8 * k + 3], (int)br[8 * k + 2]);
-                        const double ckx = __hiloint2double((int)br[8 * k + 5], (int)br[8 * k + 4]);
-                        const double cky = __hiloint2double((int)br[8 * k + 7], (int)br[8 * k + 6]);
-                        const double dr = xr[k1], di = xi[k1];
-                        const double sr = dr * csx - di * csy;
-                        const double si = dr * csy + di * csx;
-                        const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
-                        const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
-                        xr[k1] = fma(dr, ckx, fma(-di, cky, gr));
-                        xi[k1] = fma(dr, cky, fma(di, ckx, gi));
+                    for (int b = 0; b < 8; b++) {
+                        uint32_t br[32];
+                        tmem_ld32(tbsk + 32 * b, br);
+                        tmem_wait_ld();
+    #pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            const int k1 = 4 * b + k;
+                            const double csx = __hiloint2double((int)br[8 * k + 1], (int)br[8 * k + 0]);
+                            const double csy = __hiloint2double((int)br[8 * k + 3], (int)br[8 * k + 2]);
+                            const double ckx = __hiloint2double((int)br[8 * k + 5], (int)br[8 * k + 4]);
+                            const double cky = __hiloint2double((int)br[8 * k + 7], (int)br[8 * k + 6]);
+                            const double dr = xr[k1], di = xi[k1];
+                            const double sr = dr * csx - di * csy;
+                            const double si = dr * csy + di * csx;
+                            const double gr = __shfl_xor_sync(0xffffffffu, sr, 16);
+                            const double gi = __shfl_xor_sync(0xffffffffu, si, 16);
+                            xr[k1] = fma(dr, ckx, fma(-di, cky, gr));
+                            xi[k1] = fma(dr, cky, fma(di, ckx, gi));
+                        }
                     }
                 }
                 if (!(g == last_group && i == n_lwe - 1)) {
@@ -410,8 +477,21 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                     }
                 }
                 // ---- inverse row pass, conjugate twiddle, transpose back ----
-                fft32_neg(xr, xi);
-                if (kOpt & 1) {
+                if ((kOpt & 9) == 9) {
+                    uint32_t tw0[16], tw1[16];
+                    tmem_ld16(ttw0, tw0);          // in flight during the inverse row pass
+                    fft32_neg(xr, xi);
+#pragma unroll
+                    for (int c = 0; c < 8; c += 2) {
+                        wait_ld_dep16(tw0);
+                        tmem_ld16((((c + 1) & 4) ? ttw1 : ttw0) + 16 * ((c + 1) & 3), tw1);
+                        inv_twiddle4(xr, xi, tw0, 4 * c);
+                        wait_ld_dep16(tw1);
+                        if (c + 2 < 8) tmem_ld16((((c + 2) & 4) ? ttw1 : ttw0) + 16 * ((c + 2) & 3), tw0);
+                        inv_twiddle4(xr, xi, tw1, 4 * c + 4);
+                    }
+                } else if (kOpt & 1) {
+                    fft32_neg(xr, xi);
 #pragma unroll
                     for (int c = 0; c < 8; c++) {   // 4 twiddles (16 columns) per TMEM load
                         uint32_t tw[16];
@@ -428,6 +508,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         }
                     }
                 } else {
+                    fft32_neg(xr, xi);
                     const double2 *__restrict__ Tr = sm.T + rk2 * kTStride;
 #pragma unroll
                     for (int n1 = 0; n1 < 32; n1++) {
@@ -456,13 +537,8 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                     }
                 }
                 if (pass_tok) named_bar_arrive(tok_pass, 256);
-                fft32_neg(xr, xi);
-                // ---- conjugate pre-twist, add as torus into the TMEM accumulator ----
-#pragma unroll
-                for (int c = 0; c < 4; c++) {   // 8 values of m (16 coefficients) per chunk
-                    uint32_t ohi[16];
-                    tmem_ld16(tacc + 16 * c, ohi);
-                    tmem_wait_ld();
+                // ---- inverse column pass; conjugate pre-twist, add as torus into the TMEM accumulator ----
+                auto accumulate8 = [&](uint32_t (&ohi)[16], int c) {
 #pragma unroll
                     for (int mm = 0; mm < 8; mm++) {
                         const int m = 8 * c + mm;
@@ -482,6 +558,31 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                         H[lane + 32 * m + kH] = ohi[2 * mm + 1];
                     }
                     tmem_st16(tacc + 16 * c, ohi);
+                };
+                if (kOpt & 8) {
+                    uint32_t oa[16], ob[16];
+                    tmem_ld16(tacc, oa);           // in flight during the inverse column pass
+                    fft32_neg(xr, xi);
+                    wait_ld_dep16(oa);
+                    tmem_ld16(tacc + 16, ob);
+                    accumulate8(oa, 0);
+                    wait_ld_dep16(ob);
+                    tmem_ld16(tacc + 32, oa);      // issued after st16(chunk 0): same registers, in order
+                    accumulate8(ob, 1);
+                    wait_ld_dep16(oa);
+                    tmem_ld16(tacc + 48, ob);
+                    accumulate8(oa, 2);
+                    wait_ld_dep16(ob);
+                    accumulate8(ob, 3);
+                } else {
+                    fft32_neg(xr, xi);
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {   // 8 values of m (16 coefficients) per chunk
+                        uint32_t ohi[16];
+                        tmem_ld16(tacc + 16 * c, ohi);
+                        tmem_wait_ld();
+                        accumulate8(ohi, c);
+                    }
                 }
                 tmem_wait_st();
                 __syncwarp();  // hi plane of polynomial w complete before this warp's rotated reads
@@ -631,15 +732,15 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
         }
     }
     static bool knobs_read = false;
-    static int stagger = 4, opt = 5;   // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1)
+    static int stagger = 4, opt = 13;  // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1 | 5 | 13)
     if (!knobs_read) {
         knobs_read = true;
         if (const char *e = getenv("FHS_BR_STAGGER")) stagger = atoi(e);
-        if (const char *e = getenv("FHS_BR_OPT")) opt = atoi(e) & 5;
+        if (const char *e = getenv("FHS_BR_OPT")) opt = atoi(e) & 13;
     }
     if (!c->attr_br) {
 #define FHS_BR_ATTR(o, st) FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel<o, st>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem2Bytes))
-        FHS_BR_ATTR(0, 0); FHS_BR_ATTR(1, 3); FHS_BR_ATTR(5, 3);
+        FHS_BR_ATTR(0, 0); FHS_BR_ATTR(1, 3); FHS_BR_ATTR(5, 3); FHS_BR_ATTR(13, 3);
 #undef FHS_BR_ATTR
         c->attr_br = true;
     }
@@ -658,6 +759,7 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
         // FHS_BR_OPT=0 FHS_BR_STAGGER=0 selects the round-1 baseline kernel (A/B runs); default is
         // the TMEM-twiddle kernel with the stagger flag on (4); 3 = same kernel, flag off.
         kern_t kern = (opt == 0 && st == 0) ? blind_rotate_v2_kernel<0, 0>
+                      : (opt & 8)            ? blind_rotate_v2_kernel<13, 3>
                       : (opt & 4)            ? blind_rotate_v2_kernel<5, 3> : blind_rotate_v2_kernel<1, 3>;
         const int stagger_rt = st == 4;
         kern<<<(unsigned)ctas, kThreads2, kSmem2Bytes, c->stream>>>(

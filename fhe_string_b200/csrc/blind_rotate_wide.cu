@@ -76,6 +76,15 @@ __device__ __forceinline__ void w_wait_ld16(uint32_t (&r)[16]) {
                  :: "memory");
 }
 
+__device__ __forceinline__ void w_wait_ld32(uint32_t (&r)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                   "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                   "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :: "memory");
+}
+
 template <bool kConj, int kPerm, int kChunk>
 __device__ __forceinline__ void w_twiddle4(double (&xr)[16], double (&xi)[16], const uint32_t (&tw)[16]) {
 #pragma unroll
@@ -368,12 +377,12 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                 }
                 // ---- conjugate twiddle 1, inverse pass 1 ----
                 w_twiddle16<true, 4>(xr, xi, ttw1, twp);
+                uint32_t ohi[32];
+                tmem_ld32(town, ohi);               // in flight during the inverse pass
                 fft16_neg(xr, xi);
                 // ---- conjugate pre-twist, add as torus into the TMEM accumulator + hi plane ----
                 {
-                    uint32_t ohi[32];
-                    tmem_ld32(town, ohi);
-                    tmem_wait_ld();
+                    w_wait_ld32(ohi);
 #pragma unroll
                     for (int j1 = 0; j1 < 16; j1++) {
                         double ur, ui;
