@@ -73,6 +73,20 @@ struct Ops {
             for (size_t i = ch * C; i < std::min(n, (ch + 1) * C); i++) { s = add(s, v[i]); run[i] = s; }
             tot[ch] = s;  // raw sum (<= 15)
         }
+        if (nch > 1 && nch <= 16) {
+            // two levels: chunk-local prefix bits, then OR with the COUNT of non-empty earlier chunks
+            // (the chunk's own last prefix bit is its "non-empty" flag; the count stays below 16)
+            std::vector<Bool> local(n);
+            for (size_t i = 0; i < n; i++) local[i] = g.pbs(run[i], [](int x) { return x >= 1; }, 0, 1);
+            Lin before = Graph::constant(0);
+            for (size_t ch = 0; ch < nch; ch++) {
+                const size_t lo = ch * C, hi = std::min(n, (ch + 1) * C);
+                for (size_t i = lo; i < hi; i++)
+                    p[i] = ch == 0 ? local[i] : g.pbs(add(local[i], before), [](int x) { return x >= 1; }, 0, 1);
+                before = add(before, local[hi - 1]);
+            }
+            return p;
+        }
         std::vector<Bool> carry;  // OR of all chunks strictly before ch
         if (nch > 1) {
             std::vector<Bool> tb(nch - 1);
@@ -143,39 +157,44 @@ struct Ops {
     }
 
     // ---------------- ordering ----------------
-    // sign in {0: a<b, 1: a==b, 2: a>b} per packed pair, most significant pair last
+    // sign in {-1: a<b, 0: a==b, +1: a>b} per packed pair, most significant pair last: one signed PBS on
+    // the difference (negative inputs come back as -LUT[x+16], the negacyclic convention)
     std::vector<Lin> sign_pairs(const std::vector<Lin> &pa, const std::vector<Lin> &pb) {
         std::vector<Lin> s;
-        for (size_t i = 0; i < pa.size(); i++) {
-            Lin d = g.pbs(sub(pa[i], pb[i]), [](int x) { return x == 0 ? 0 : 1; }, -1, 1, true);
-            s.push_back(bounded(addc(d, 1), 0, 2));
-        }
+        for (size_t i = 0; i < pa.size(); i++)
+            s.push_back(g.pbs(sub(pa[i], pb[i]), [](int x) { return x == 0 ? 0 : 1; }, -1, 1, true));
         return s;
     }
-    // reduce signs (index 0 least significant) to one sign, then map through `fin`
+    // Reduce signs (index 0 least significant) to one and map it through `fin` (argument 0: less,
+    // 1: equal, 2: greater).  Four signs at a time: 8 s3 + 4 s2 + 2 s1 + s0 lies in [-15, 15] and has
+    // the sign of the most significant non-zero s_k, so the same signed sign-LUT combines them
+    // (log4 depth; the pairwise 3*hi+lo scheme needed log2).  The last <= 3 signs are shifted to an
+    // unsigned value and go through `fin` directly.
     Bool reduce_sign(std::vector<Lin> s, std::function<int(int)> fin) {
         if (s.empty()) return Graph::constant(fin(1));
-        while (s.size() > 1) {
+        while (s.size() > 3) {
             std::vector<Lin> nx;
-            size_t i = 0;
-            for (; i + 1 < s.size(); i += 2) {
-                Lin x = add(scale(s[i + 1], 3), s[i]);  // hi*3 + lo <= 8
-                if (s.size() == 2) {
-                    return g.pbs(x, [fin](int v) { int hi = v / 3, lo = v % 3; return fin(hi == 1 ? lo : hi); }, 0, 1);
-                }
-                nx.push_back(g.pbs(x, [](int v) { int hi = v / 3, lo = v % 3; return hi == 1 ? lo : hi; }, 0, 2));
+            for (size_t i = 0; i < s.size(); i += 4) {
+                const size_t n = std::min<size_t>(4, s.size() - i);
+                if (n == 1) { nx.push_back(s[i]); continue; }
+                Lin x = Graph::constant(0);
+                for (size_t k = 0; k < n; k++) x = add(x, scale(s[i + k], 1 << k));
+                nx.push_back(g.pbs(x, [](int v) { return v == 0 ? 0 : 1; }, -1, 1, true));
             }
-            if (i < s.size()) nx.push_back(s[i]);
             s.swap(nx);
         }
-        return g.pbs(s[0], [fin](int v) { return fin(v); }, 0, 1);
+        Lin x = Graph::constant(0);
+        int off = 0;
+        for (size_t k = 0; k < s.size(); k++) { x = add(x, scale(s[k], 1 << k)); off += 1 << k; }
+        x = bounded(addc(x, off), 0, 2 * off);
+        return g.pbs(x, [fin, off](int v) { const int d = v - off; return fin(d < 0 ? 0 : (d == 0 ? 1 : 2)); }, 0, 1);
     }
     // generic comparison with final map fin(sign)
     Bool cmp(const Rad &a, const Rad &b, std::function<int(int)> fin) {
         return reduce_sign(sign_pairs(pack(a), pack(b)), fin);
     }
     Bool cmp_scalar(const Rad &a, uint64_t c, std::function<int(int)> fin) {
-        if (!scalar_fits(c, a.size())) return Graph::constant(fin(0));  // a < c always
+        if (!scalar_fits(c, a.size())) return Graph::constant(fin(0));  // a < c always (fin(0) = "less")
         std::vector<int> pc = pack_scalar(c, a.size());
         std::vector<Lin> pb;
         for (int v : pc) pb.push_back(Graph::constant(v));
@@ -228,20 +247,32 @@ struct Ops {
         for (size_t i = 1; i < nblocks; i++) r.push_back(Graph::constant(0));
         return r;
     }
-    // Sum of radix values of which AT MOST ONE is non-zero (one-hot selections): linear, with an
-    // identity-LUT refresh whenever the variance of the running sum would exceed 160 PBS outputs.
+    // Sum of radix values of which AT MOST ONE is non-zero (one-hot selections).  Linear; where the
+    // variance of a digit's sum would exceed 160 PBS outputs the terms are cut into groups below that
+    // bound, every group is refreshed by an identity LUT IN THE SAME LEVEL and the fresh group sums are
+    // added (a running sum with refreshes along the way would cost one level per refresh).
     Rad onehot_sum(const std::vector<Rad> &v, size_t nblocks) {
-        Rad acc = scalar(0, nblocks);
-        for (auto &r : v) {
-            for (size_t i = 0; i < nblocks; i++) {
-                if (acc[i].noise + r[i].noise > 160.f)
-                    acc[i] = g.pbs(acc[i], [](int x) { return x & 3; }, 0, 3);
-                acc[i] = bounded(add(acc[i], r[i]), 0, 3);
+        Rad acc(nblocks);
+        for (size_t i = 0; i < nblocks; i++) {
+            std::vector<Lin> groups;
+            Lin cur = Graph::constant(0);
+            for (auto &r : v) {
+                if (r[i].is_const() && r[i].c == 0) continue;
+                if (cur.noise + r[i].noise > 160.f) { groups.push_back(cur); cur = Graph::constant(0); }
+                cur = bounded(add(cur, r[i]), 0, 3);
             }
-        }
-        // callers pack / subtract the result (variance x17 .. x34): hand back fresh digits
-        for (size_t i = 0; i < nblocks; i++)
+            if (groups.empty()) {
+                acc[i] = cur;
+            } else {
+                groups.push_back(cur);
+                Lin sum = Graph::constant(0);
+                for (auto &gsum : groups)
+                    sum = bounded(add(sum, g.pbs(gsum, [](int x) { return x & 3; }, 0, 3)), 0, 3);
+                acc[i] = sum;
+            }
+            // callers pack / subtract the result (variance x17 .. x34): hand back fresh digits
             if (acc[i].noise > 10.f) acc[i] = g.pbs(acc[i], [](int x) { return x & 3; }, 0, 3);
+        }
         return acc;
     }
 

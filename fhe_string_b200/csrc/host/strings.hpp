@@ -147,7 +147,8 @@ struct StrOps : Ops {
         std::vector<Bool> p = prefix_or(w);
         std::vector<Rad> terms;
         for (size_t k = 0; k < w.size(); k++) {
-            Bool first = (k == 0) ? w[0] : g.pbs(add(w[k], bnot(p[k - 1])), [](int x) { return x == 2; }, 0, 1);
+            // the prefix OR is monotone, so "first set position" is its discrete derivative: no PBS
+            Bool first = (k == 0) ? p[0] : bounded(sub(p[k], p[k - 1]), 0, 1);
             size_t idx = reverse ? w.size() - 1 - k : k;
             terms.push_back(bool_times_scalar(first, idx, nb_usize));
         }
