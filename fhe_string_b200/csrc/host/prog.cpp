@@ -403,7 +403,27 @@ extern "C" int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_insta
         else if (g.nodes[i].kind == K_LIN) lin_at[g.nodes[i].level].push_back((int32_t)i);
     }
     for (auto &v : pbs_at) gmax = std::max(gmax, v.size());
-    const size_t Mc = std::max<size_t>(1, std::min(M, kManyChunk / gmax));
+    // Chunk size: at most kManyChunk evaluations in the largest level, and among those sizes the one
+    // that minimises (number of chunks) x (blind-rotation rounds per chunk).  A round is 4 ciphertexts
+    // per SM (592 on a B200); a remainder of <= 148 / <= 296 goes to the wide kernel at 0.39 / 0.59 of
+    // a round.  A short last chunk still runs whole levels, so equal chunks beat "full chunks + a rest".
+    const size_t Mc_max = std::max<size_t>(1, std::min(M, kManyChunk / gmax));
+    size_t Mc = Mc_max;
+    {
+        constexpr size_t kRound = 592;
+        double best = -1.0;
+        for (size_t cand = Mc_max; cand >= std::max<size_t>(1, Mc_max / 2); cand--) {
+            double rounds = 0.0;
+            for (auto &v : pbs_at) {
+                if (v.empty()) continue;
+                const size_t rows = v.size() * cand, rem = rows % kRound;
+                rounds += (double)(rows / kRound) + (rem == 0 ? 0.0 : rem <= 148 ? 0.39 : rem <= 296 ? 0.59 : 1.0);
+            }
+            const double cost = rounds * (double)((M + cand - 1) / cand);
+            if (best < 0.0 || cost < best) { best = cost; Mc = cand; }
+            if (cand == 1) break;
+        }
+    }
     // ---- plan for one chunk of Mc instances: slot(node, m) = base[node] + m * stride[node] ----
     std::vector<size_t> base(N, 0), stride(N, 0);
     size_t n_in = 0;
