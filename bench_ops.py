@@ -140,15 +140,22 @@ def main():
             for a, b in pairs:
                 inb.append(np.concatenate([ckr.encrypt_str(a, 64).blocks, ckr.encrypt_str(b, 64).blocks]))
             inb = np.stack(inb) if inb else np.zeros((0, prog.n_inputs, eng.big), np.uint64)
-            barrier()
-            t0 = time.perf_counter()
-            out, st = prog.run_many(eng, inb)
-            torch.cuda.synchronize()
-            dt = max_over_ranks((time.perf_counter() - t0) * 1e3)
+            # pinned host memory, as for bench.py's e2e leg: 8.7 GB of input blocks cross PCIe
+            pin = torch.empty(inb.shape, dtype=torch.int64, pin_memory=True)
+            pin.numpy().view(np.uint64)[...] = inb
+            inb = pin.numpy().view(np.uint64)
+            all_ms = []
+            for _ in range(2):      # the first call also grows the device memory pool (GBs of ciphertext pools)
+                barrier()
+                t0 = time.perf_counter()
+                out, st = prog.run_many(eng, inb)
+                torch.cuda.synchronize()
+                all_ms.append(round(max_over_ranks((time.perf_counter() - t0) * 1e3), 1))
+            dt = min(all_ms)
             got = [bool(ckr.decrypt_blocks(out[m, :1])[0]) for m in range(len(pairs))]
             want = [(a == b) if op == "eq" else (a < b) for a, b in pairs]
             ok = max_over_ranks(0.0 if got == want else 1.0) == 0.0
-            sweep[op] = {"ms": dt, "pairs": M, "lut_evals": prog.pbs_count * M, "levels": prog.depth,
+            sweep[op] = {"ms": dt, "all_ms": all_ms, "pairs": M, "lut_evals": prog.pbs_count * M, "levels": prog.depth,
                          "comparisons_per_s": M / dt * 1e3, "pbs_per_s": prog.pbs_count * M / dt * 1e3,
                          "correct": ok}
         result["config5_1024_comparisons"] = sweep
