@@ -274,3 +274,20 @@ def test_hypothesis_generated_ascii_strings():
         assert run("split_ascii_whitespace", [s], [ps]) == s.split()
 
     check()
+
+
+def test_ordering_long_strings_first_difference_everywhere():
+    """Fan-in-4 signed sign reduction (radix.hpp reduce_sign) on 40-char strings: the first difference
+    at every depth of the reduction tree, both directions, plus prefix / equal cases."""
+    rng = random.Random(11)
+    base = "".join(rng.choice("abcdefghijklmnopqrstuvwxyz") for _ in range(40))
+    cases = [(base, base), (base, base[:-1]), (base[:-1], base), (base, base + "a"), ("", base), (base, "")]
+    for pos in (0, 1, 3, 4, 7, 15, 16, 31, 39):
+        for delta in (-1, 1):
+            other = base[:pos] + chr(ord(base[pos]) + delta) + "".join(rng.choice("az") for _ in range(39 - pos))
+            cases.append((base, other))
+    for a, b in cases:
+        assert run("lt", [a, b], [44, 41]) == (a < b), (a, b)
+        assert run("le", [a, b], [44, 41]) == (a <= b), (a, b)
+        assert run("gt", [a, b], [44, 41]) == (a > b), (a, b)
+        assert run("ge", [a, b], [44, 41]) == (a >= b), (a, b)
