@@ -119,3 +119,21 @@ def test_add_insert_repeat(engine, keyset):
     vals = to_blocks(chars[0]) + usize_blocks(3)
     out, _ = p.run(engine, keyset.encrypt(np.array(vals, dtype=np.uint64), seed=9))
     assert decode(p.desc, [int(x) for x in keyset.decrypt(out)]) == pat * 3
+
+
+def test_split_long_overlapping_under_noise(engine, keyset):
+    """The chunked (speculative) non-overlapping match selection, the last-set scan and the fan-in-4
+    sign reduction on real ciphertexts: 40-char strings padded to 48, matches overlapping in every phase."""
+    s = "ab" * 10 + "aabaabaab" + "xyzxyzxyzab"
+    for pat, pp in (("aba", 5), ("ab", None), ("aab", 8)):
+        assert run_gpu(engine, keyset, "split", [s, pat], [48, pp])[0] == s.split(pat)
+        assert run_gpu(engine, keyset, "rsplit", [s, pat], [48, pp])[0] == s.rsplit(pat)[::-1]
+    assert run_gpu(engine, keyset, "splitn", [s, "ab"], [48, 4], usizes=[3])[0] == s.split("ab", 2)
+    assert run_gpu(engine, keyset, "split", [s, "b"], [48, None])[0] == s.split("b")
+    f = s.find("xyzab")
+    assert run_gpu(engine, keyset, "find", [s, "xyzab"], [48, 8])[0] == f
+    assert run_gpu(engine, keyset, "rfind", [s, "ab"], [48, 8])[0] == s.rfind("ab")
+    t = s[:30] + "b" + s[31:]
+    for a, b in ((s, t), (t, s), (s, s), (s[:20], s)):
+        assert run_gpu(engine, keyset, "lt", [a, b], [48, 48])[0] == (a < b)
+        assert run_gpu(engine, keyset, "ge", [a, b], [48, 48])[0] == (a >= b)
