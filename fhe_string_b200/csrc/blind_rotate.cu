@@ -18,8 +18,8 @@
 // frequencies k2 in [16w, 16w+16) of BOTH polynomials (lanes 0-15: poly 0, lanes 16-31: poly 1), so
 // the 2x2 GGSW contraction needs only one shfl_xor(16) exchange per frequency.
 //
-// A CTA holds kCtPerCta ciphertext slots that share the twiddle table; slots synchronise with
-// named barriers (64 threads) and fetch ciphertexts from a global work counter (persistent CTAs).
+// A CTA holds kSlots2 ciphertext slots that share the twiddle table; the two warps of a slot
+// synchronise with a named barrier (64 threads); CTAs are persistent and stride over slot groups.
 #include <cstdlib>
 
 #include "fhs_internal.cuh"
@@ -29,59 +29,13 @@
 namespace fhs {
 namespace {
 
-constexpr int kCtPerCta = 3;
-constexpr int kThreads = 64 * kCtPerCta;
 constexpr int kTile = 32 * kTStride;  // complex elements in one padded 32x32 tile
-constexpr int kBskRing = 8;           // BSK frequency rows in flight per thread (register ring)
 
 __constant__ double kPreRe[32] = FHS_PRETWIST_RE;
 __constant__ double kPreIm[32] = FHS_PRETWIST_IM;
 
-struct SlotSmem {
-    uint64_t acc[2][kN];     // accumulator GLWE: [0] mask polynomial, [1] body polynomial
-    double2 S[2][kTile];     // transpose tiles, one per polynomial: S[p][k2 * 33 + n1]
-    uint16_t amod[768];      // modulus-switched mask elements of the current ciphertext
-    unsigned int cur;        // index of the current ciphertext
-    unsigned int pad[3];
-};
-struct Smem {
-    double2 T[kTile];        // T[k2 * 33 + n1] = e^{2 pi i n1 (k2 + 1/4) / 1024}
-    SlotSmem slot[kCtPerCta];
-};
-static_assert(sizeof(Smem) <= 227 * 1024, "shared memory budget");
-
 __device__ __forceinline__ void slot_bar(int slot) {
     asm volatile("bar.sync %0, 64;" ::"r"(slot + 1) : "memory");
-}
-
-// Streaming 16-byte BSK load.  asm volatile keeps the compiler from sinking the prefetch below the
-// barrier it is issued in front of (the point of the ring is to overlap L2 latency).
-__device__ __forceinline__ double2 ldg_stream(const double2 *p) {
-    double2 v;
-    asm volatile("ld.volatile.global.v2.f64 {%0, %1}, [%2];"
-                 : "=d"(v.x), "=d"(v.y)
-                 : "l"(p));
-    return v;
-}
-
-// exact int32 -> double without the conversion pipe
-__device__ __forceinline__ double int_to_double(int d) {
-    return __hiloint2double(0x43300000, d ^ (int)0x80000000) - 4503601774854144.0;
-}
-
-// tfhe SignedDecomposer(base_log 23, level 1): closest representable, then one signed digit in
-// [-2^22, 2^22].
-__device__ __forceinline__ int pbs_digit(uint64_t x) {
-    const uint32_t hi = (uint32_t)(x >> 32);
-    const uint32_t s = (((hi >> 8) + 1u) >> 1) & 0x7FFFFFu;
-    return (int)s - (int)((s > 0x400000u) ? 0x800000u : 0u);
-}
-
-// Value in integer torus units (|v| < 2^115) -> v mod 2^64, rounded to nearest.
-__device__ __forceinline__ uint64_t f64_to_torus(double v) {
-    const double M = 1.24615124604835863e35;  // 1.5 * 2^116: ulp = 2^64
-    const double r = (v + M) - M;             // v rounded to a multiple of 2^64
-    return (uint64_t)__double2ll_rn(v - r);   // exact difference in [-2^63, 2^63]
 }
 
 // a1.5 pbs_modulus_switch for N = 2048: ((x >> 51) + 1) >> 1, reduced mod 2N.

@@ -2,6 +2,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -261,7 +262,14 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
             rc = fhs::cuda_fail(e, "cudaMemcpyAsync(bsk)");
             break;
         }
-        if ((rc = fhs::launch_bsk_transform(c, d_raw)) != FHS_OK) break;
+        {
+            // Fourier BSK rounded once from a double-double transform (bsk_fourier.cu); the f64
+            // transform that shares the hot loop's FFT code stays selectable for A/B noise runs
+            const char *xf = getenv("FHS_BSK_XF");
+            const bool f64_only = xf && atoi(xf) == 0;
+            if ((rc = f64_only ? fhs::launch_bsk_transform(c, d_raw) : fhs::launch_bsk_transform_dd(c, d_raw)) != FHS_OK)
+                break;
+        }
         if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "bsk transform");
             break;

@@ -112,3 +112,23 @@ def test_pbs_noise_matches_estimate(keyset):
     assert np.array_equal(keyset.decrypt(out), msgs)
     err = keyset.phase_error(out, msgs)
     assert np.std(err) < 4e-5 and np.abs(err).max() < 2.0**-10
+
+
+def test_noise_golden_matches_live_oracle(keyset):
+    """tests/golden/noise_golden.json (32 768 oracle KS-PBS, make_noise_golden.py) is the reference of
+    the GPU noise tier; a small live sample must agree with it within its own sampling error."""
+    import json
+    from conftest import bench_tables
+    gold = json.load(open(os.path.join(os.path.dirname(GOLD), "noise_golden.json")))
+    assert gold["n_samples"] >= 30000 and abs(gold["mean"]) < 1e-6
+    tables = bench_tables()
+    m = 96
+    rng = np.random.default_rng(21)
+    msgs = rng.integers(0, 16, m)
+    cts = keyset.encrypt(msgs, seed=21)
+    lid = (np.arange(m) % 8).astype(np.uint32)
+    out = keyset.ks_pbs_batch(cts, lid, tables)
+    want = tables[lid, msgs]
+    assert np.array_equal(keyset.decrypt(out), want)
+    var = float(np.var(keyset.phase_error(out, want)))
+    assert 0.55 * gold["variance"] < var < 1.6 * gold["variance"], (var, gold["variance"])

@@ -1,4 +1,7 @@
 """GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on seeded inputs."""
+import json
+import os
+
 import numpy as np
 import pytest
 
@@ -147,14 +150,21 @@ def test_noise_variance_1e5_samples(engine, keyset):
     total = n * reps
     assert total >= 100_000
     var_gpu = s2 / total - (s1 / total) ** 2
-    # oracle reference variance on a bounded sample (CPU PBS is ~3 ms each per core)
+    # oracle reference: 32 768 samples of the same workload, computed offline by
+    # tests/golden/make_noise_golden.py (the oracle is the same algorithm class as tfhe-rs 0.5: f64
+    # negacyclic FFT, 64-bit accumulator).  "No worse" = not above it by more than 3 standard errors
+    # of the two sample variances (0.78 % and 0.44 %).
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "noise_golden.json")))
+    var_ref = gold["variance"]
+    se = (gold["variance_rel_std_error"] ** 2 + 2.0 / total) ** 0.5
+    assert var_gpu <= var_ref * (1.0 + 3.0 * se), (var_gpu, var_ref)
+    # a live cross-check of the committed figure on a small oracle sample (+-10 %)
     m = 192
     msgs, cts = _mixed_inputs(keyset, m, 77)
     lid = (np.arange(m) % 8).astype(np.uint32)
     ref = keyset.ks_pbs_batch(cts, lid, tables)
-    var_ref = float(np.var(keyset.phase_error(ref, tables[lid, msgs])))
-    # sample variance of 192 draws has ~10 % relative std; allow 1.35x
-    assert var_gpu <= 1.35 * var_ref, (var_gpu, var_ref)
+    var_live = float(np.var(keyset.phase_error(ref, tables[lid, msgs])))
+    assert 0.65 * var_ref < var_live < 1.45 * var_ref, (var_live, var_ref)
     assert var_gpu ** 0.5 < 3.2e-5
     assert abs(s1 / total) < 1e-6          # unbiased
     assert worst < 2.0 ** -9
@@ -189,3 +199,41 @@ def test_keyswitch_baseline_kernels(variant):
     env = dict(os.environ, FHS_KS_VARIANT=variant)
     r = subprocess.run([sys.executable, "-c", _VARIANT_SCRIPT, root], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "variant ok" in r.stdout, r.stderr[-2000:]
+
+
+_BSK_XF_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+import fhe_string_b200 as F
+from oracle import oracle as O
+from conftest import bench_tables
+ks = O.Keyset(seed=1)
+eng = F.Engine(0)
+eng.upload_keys(ks.p, ks.ksk(), ks.bsk(), ksk_level_order=0)
+tabs = bench_tables()
+rng = np.random.default_rng(8)
+n = 2048
+msgs = rng.integers(0, 16, n)
+lut_id = (np.arange(n) % 8).astype(np.uint32)
+out = eng.ks_pbs(ks.encrypt(msgs, seed=8), lut_id, tabs)
+want = tabs[lut_id, msgs]
+assert np.array_equal(ks.decrypt(out), want)
+print("sigma", float(np.std(ks.phase_error(out, want))))
+"""
+
+
+def test_bsk_transform_f64_variant_is_noisier_but_correct():
+    """fhs_upload_keys rounds the Fourier BSK once from a double-double transform (bsk_fourier.cu).
+    FHS_BSK_XF=0 keeps the plain f64 transform (the hot loop's own FFT code): same decryptions,
+    measurably more output noise (2.71e-5 vs 2.52e-5 over 32 768 samples)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sig = {}
+    for xf in ("0", "1"):
+        env = dict(os.environ, FHS_BSK_XF=xf)
+        r = subprocess.run([sys.executable, "-c", _BSK_XF_SCRIPT, root], env=env, capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0 and "sigma" in r.stdout, r.stderr[-2000:]
+        sig[xf] = float(r.stdout.split("sigma")[1])
+    assert sig["1"] < sig["0"] < 3.2e-5, sig
