@@ -63,6 +63,18 @@ __device__ __forceinline__ dd dd_from_i64(uint64_t x) {
 }
 
 constexpr int kDdThreads = 256;
+// 2^-10 (inverse FFT normalisation) * 2^-34 (accumulator unit): a power of two, exact
+constexpr double kStoreScale = 1.0 / 1024.0 / 17179869184.0;
+
+// X[K] of polynomial (GGSW i, row r, column c) -> its place in the two kernel layouts
+__device__ __forceinline__ void store_bsk_value(double2 *__restrict__ bsk_f, double2 *__restrict__ bsk_w,
+                                                int i, int r, int c, int K, double2 val) {
+    const int k1 = K >> 5, k2 = K & 31;
+    const int ww = k2 >> 4, lp = (r << 4) | (k2 & 15), sl = (c == r) ? 1 : 0;
+    bsk_f[((((size_t)i * 32 + k1) * 2 + ww) * 32 + lp) * 2 + sl] = val;
+    const int cc = K & 127, f = 8 * (cc >> 6) + (K >> 7), qq = cc & 63;
+    bsk_w[((((size_t)i * 16 + f) * 4 + (qq >> 4)) * 32 + ((r << 4) | (qq & 15))) * 2 + sl] = val;
+}
 
 // one CTA per polynomial q = ((i * 2 + r) * 2 + c): GGSW i, row r, column c
 __global__ void __launch_bounds__(kDdThreads)
@@ -90,15 +102,26 @@ bsk_transform_dd_kernel(const uint64_t *__restrict__ bsk, double2 *__restrict__ 
         }
         __syncthreads();
     }
-    const double sc = 1.0 / 1024.0 / 17179869184.0;
     for (int K = threadIdx.x; K < kH; K += kDdThreads) {
         // after renormalisation hi is the f64 nearest to hi + lo
-        const double2 val = make_double2(x[K].re.hi * sc, x[K].im.hi * sc);
-        const int k1 = K >> 5, k2 = K & 31;
-        const int ww = k2 >> 4, lp = (r << 4) | (k2 & 15), sl = (c == r) ? 1 : 0;
-        bsk_f[((((size_t)i * 32 + k1) * 2 + ww) * 32 + lp) * 2 + sl] = val;
-        const int cc = K & 127, f = 8 * (cc >> 6) + (K >> 7), qq = cc & 63;
-        bsk_w[((((size_t)i * 16 + f) * 4 + (qq >> 4)) * 32 + ((r << 4) | (qq & 15))) * 2 + sl] = val;
+        store_bsk_value(bsk_f, bsk_w, i, r, c, K, make_double2(x[K].re.hi * kStoreScale, x[K].im.hi * kStoreScale));
+    }
+}
+
+// Fourier-domain import (fhs_upload_keys_fourier): the caller already holds the spectra (tfhe-rs keeps
+// only the Fourier BSK inside its ServerKey), natural frequency order, un-normalised integer units.
+//   conj_index = 0:  in[m] = sum_j z_j e^{i pi j / N} e^{+2 pi i j m / (N/2)}   (this library's own K)
+//   conj_index = 1:  in[m] = sum_j z_j e^{i pi j / N} e^{-2 pi i j m / (N/2)}   (forward DFT with the
+//                    usual negative exponent after the same twist: the same roots, visited as K = -m)
+__global__ void __launch_bounds__(kDdThreads)
+bsk_import_fourier_kernel(const double2 *__restrict__ in, double2 *__restrict__ bsk_f,
+                          double2 *__restrict__ bsk_w, int conj_index) {
+    const int q = blockIdx.x;
+    const int i = q >> 2, r = (q >> 1) & 1, c = q & 1;
+    for (int K = threadIdx.x; K < kH; K += kDdThreads) {
+        const int m = conj_index ? ((kH - K) & (kH - 1)) : K;
+        const double2 v = in[(size_t)q * kH + m];
+        store_bsk_value(bsk_f, bsk_w, i, r, c, K, make_double2(v.x * kStoreScale, v.y * kStoreScale));
     }
 }
 
@@ -137,6 +160,15 @@ int launch_bsk_transform_dd(Ctx *c, const uint64_t *d_bsk_std) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);   // `h` and `d_tab` go out of scope
     cudaFree(d_tab);
     if (e != cudaSuccess) return cuda_fail(e, "bsk transform (double-double)");
+    return FHS_OK;
+}
+
+int launch_bsk_import_fourier(Ctx *c, const double2 *d_bsk_fourier, int conj_index) {
+    bsk_import_fourier_kernel<<<(unsigned)c->n * 4, kDdThreads, 0, c->stream>>>(d_bsk_fourier, c->d_bsk_f,
+                                                                                 c->d_bsk_w, conj_index);
+    c->launches++;
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "bsk import (fourier)");
     return FHS_OK;
 }
 

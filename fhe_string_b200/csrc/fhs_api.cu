@@ -195,10 +195,15 @@ int fhs_ctx_get_params(fhs_ctx *h, fhs_params *out) {
     return FHS_OK;
 }
 
-int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
-                    const uint64_t *bsk) {
+// bsk_format: -1 = standard domain (u64 coefficients), else an FHS_FOURIER_* frequency convention
+static int upload_keys_impl(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
+                            const void *bsk, int bsk_format) {
     if (!h || !p || !ksk || !bsk) {
         fhs::set_error("fhs_upload_keys: null argument");
+        return FHS_ERR_INVALID;
+    }
+    if (bsk_format != -1 && bsk_format != FHS_FOURIER_NATURAL_POS && bsk_format != FHS_FOURIER_NATURAL_NEG) {
+        fhs::set_error("bad fourier_convention");
         return FHS_ERR_INVALID;
     }
     Ctx *c = reinterpret_cast<Ctx *>(h);
@@ -262,7 +267,12 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
             rc = fhs::cuda_fail(e, "cudaMemcpyAsync(bsk)");
             break;
         }
-        {
+        if (bsk_format != -1) {
+            // spectra computed by the caller (f64, 8 bytes per real: same size as the standard key)
+            if ((rc = fhs::launch_bsk_import_fourier(c, reinterpret_cast<const double2 *>(d_raw),
+                                                     bsk_format == FHS_FOURIER_NATURAL_NEG)) != FHS_OK)
+                break;
+        } else {
             // Fourier BSK rounded once from a double-double transform (bsk_fourier.cu); the f64
             // transform that shares the hot loop's FFT code stays selectable for A/B noise runs
             const char *xf = getenv("FHS_BSK_XF");
@@ -282,6 +292,16 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
     }
     c->has_keys = true;
     return FHS_OK;
+}
+
+int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
+                    const uint64_t *bsk) {
+    return upload_keys_impl(h, p, ksk, ksk_level_order, bsk, -1);
+}
+
+int fhs_upload_keys_fourier(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
+                            const double *bsk_fourier, int fourier_convention) {
+    return upload_keys_impl(h, p, ksk, ksk_level_order, bsk_fourier, fourier_convention);
 }
 
 static int check_batch_args(Ctx *c, const void *a, const void *b, const void *t, const void *o,

@@ -76,6 +76,8 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
 int launch_bsk_transform(Ctx *c, const uint64_t *d_bsk_std);
 // bsk_fourier.cu: the same transform in double-double arithmetic (default; FHS_BSK_XF=0 selects the f64 one)
 int launch_bsk_transform_dd(Ctx *c, const uint64_t *d_bsk_std);
+// bsk_fourier.cu: spectra supplied by the caller in natural frequency order (fhs_upload_keys_fourier)
+int launch_bsk_import_fourier(Ctx *c, const double2 *d_bsk_fourier, int conj_index);
 // blind_rotate_wide.cu: 4 warps per ciphertext, for levels of at most 2 ciphertexts per SM
 int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                              const uint64_t *d_tables, size_t batch, uint64_t *d_out);

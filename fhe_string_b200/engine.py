@@ -23,9 +23,13 @@ class Params(ctypes.Structure):
 
 
 # every symbol include/fhs_cuda.h declares
+# include/fhs_cuda.h FHS_FOURIER_*: exponent sign of a caller-supplied Fourier BSK
+FOURIER_NATURAL_POS = 0
+FOURIER_NATURAL_NEG = 1
+
 EXPORTS = [
     "fhs_default_params", "fhs_last_error", "fhs_version", "fhs_ctx_create", "fhs_ctx_destroy",
-    "fhs_ctx_set_stream", "fhs_ctx_synchronize", "fhs_upload_keys", "fhs_ks_pbs_batch",
+    "fhs_ctx_set_stream", "fhs_ctx_synchronize", "fhs_upload_keys", "fhs_upload_keys_fourier", "fhs_ks_pbs_batch",
     "fhs_ks_pbs_batch_dev", "fhs_keyswitch_batch", "fhs_keyswitch_batch_dev", "fhs_build_lut",
     "fhs_pbs_batch", "fhs_pbs_batch_dev", "fhs_last_kernel_ms", "fhs_launch_count",
     "fhs_measure_fp64_tflops",
@@ -59,6 +63,7 @@ def load_library():
     L.fhs_ctx_set_stream.argtypes = [vp, vp]
     L.fhs_ctx_synchronize.argtypes = [vp]
     L.fhs_upload_keys.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, vp]
+    L.fhs_upload_keys_fourier.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, vp, ctypes.c_int]
     L.fhs_ks_pbs_batch.argtypes = [vp, vp, vp, vp, sz, sz, vp]
     L.fhs_ks_pbs_batch_dev.argtypes = [vp, vp, vp, vp, sz, sz, vp]
     L.fhs_keyswitch_batch.argtypes = [vp, vp, sz, vp]
@@ -123,6 +128,23 @@ class Engine:
         assert ksk.size == big * p.ks_level * (p.lwe_dim + 1), "ksk size"
         assert bsk.size == p.lwe_dim * p.pbs_level * (p.glwe_dim + 1) ** 2 * p.poly_size, "bsk size"
         self._check(self.L.fhs_upload_keys(self.h, ctypes.byref(p), kp, int(ksk_level_order), bp))
+        self._keys_uploaded(p, big)
+
+    def upload_keys_fourier(self, params, ksk, bsk_fourier, ksk_level_order=0, convention=FOURIER_NATURAL_NEG):
+        """fhs_upload_keys_fourier: `bsk_fourier` complex128 [n][level][k+1][k+1][N/2], natural order."""
+        p = Params()
+        for name, _ in Params._fields_:
+            setattr(p, name, int(getattr(params, name)))
+        ksk, kp = _np(ksk, np.uint64)
+        bf = np.ascontiguousarray(bsk_fourier, dtype=np.complex128)
+        big = p.glwe_dim * p.poly_size
+        assert ksk.size == big * p.ks_level * (p.lwe_dim + 1), "ksk size"
+        assert bf.size == p.lwe_dim * p.pbs_level * (p.glwe_dim + 1) ** 2 * p.poly_size // 2, "bsk size"
+        self._check(self.L.fhs_upload_keys_fourier(self.h, ctypes.byref(p), kp, int(ksk_level_order),
+                                                   bf.ctypes.data_as(ctypes.c_void_p), int(convention)))
+        self._keys_uploaded(p, big)
+
+    def _keys_uploaded(self, p, big):
         self.p = p
         self.big = big + 1
         self.small = p.lwe_dim + 1

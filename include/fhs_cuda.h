@@ -53,6 +53,15 @@ typedef struct fhs_ctx fhs_ctx;
 #define FHS_KSK_LEVEL_MSB_FIRST 0 /* rows stored level 1 (most significant) .. level l  (tfhe-rs 0.5) */
 #define FHS_KSK_LEVEL_LSB_FIRST 1 /* rows stored level l .. level 1 */
 
+/* Frequency convention of a caller-supplied Fourier BSK (fhs_upload_keys_fourier).  With
+ * z_j = p_j + i p_{j+N/2} (coefficients as signed 64-bit integers) and the twist w^j, w = e^{i pi/N}:
+ *   POS: X[m] = sum_j z_j w^j e^{+2 pi i j m/(N/2)}  = P(e^{i pi (4m+1)/N})
+ *   NEG: X[m] = sum_j z_j w^j e^{-2 pi i j m/(N/2)}  = P(e^{i pi (1-4m)/N})   (twist, then a forward DFT
+ *        with the usual negative exponent: what tfhe-rs' canonical/serialized order is recalled to be)
+ * Both are un-normalised and in natural order m = 0..N/2-1. */
+#define FHS_FOURIER_NATURAL_POS 0
+#define FHS_FOURIER_NATURAL_NEG 1
+
 void fhs_default_params(fhs_params *p);
 const char *fhs_last_error(void);
 int fhs_version(void);
@@ -76,6 +85,15 @@ int fhs_ctx_get_params(fhs_ctx *ctx, fhs_params *out);
  * consumes; the KSK is re-tiled to digit order. */
 int fhs_upload_keys(fhs_ctx *ctx, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
                     const uint64_t *bsk);
+/* Same, for a caller that only holds the Fourier-domain key: tfhe::integer::ServerKey keeps a
+ * FourierLweBootstrapKey and drops the standard one at key generation (src/lib.rs:64-72 returns only
+ * that ServerKey), so a reference-made server key can be uploaded without the client key.
+ *   bsk_fourier : f64 pairs (re, im) [n][pbs_level][k+1][k+1][N/2], natural frequency order,
+ *                 un-normalised (integer units of the torus), `fourier_convention` = FHS_FOURIER_*.
+ * The spectra are used as they are (scaled by a power of two and re-tiled); PBS output noise is then
+ * that of the caller's f64 transform instead of this library's double-double one. */
+int fhs_upload_keys_fourier(fhs_ctx *ctx, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
+                            const double *bsk_fourier, int fourier_convention);
 
 /* One level of independent LUT evaluations, host buffers (copies inside the call).
  * Replaces B calls of shortint apply_lookup_table (tfhe keyswitch_programmable_bootstrap_assign),

@@ -237,3 +237,57 @@ def test_bsk_transform_f64_variant_is_noisier_but_correct():
         assert r.returncode == 0 and "sigma" in r.stdout, r.stderr[-2000:]
         sig[xf] = float(r.stdout.split("sigma")[1])
     assert sig["1"] < sig["0"] < 3.2e-5, sig
+
+
+def _fourier_bsk(keyset, negative_exponent):
+    """Natural-order spectra of the standard BSK in plain f64 (numpy), the way a caller that only
+    holds a Fourier-domain key would have them: z_j = p_j + i p_{j+N/2}, twist e^{i pi j/N}, then a
+    length-N/2 DFT with exponent sign +/-, un-normalised (include/fhs_cuda.h FHS_FOURIER_*)."""
+    p = keyset.p
+    N = int(p.poly_size)
+    h = N // 2
+    polys = np.ascontiguousarray(keyset.bsk()).view(np.int64).reshape(-1, N).astype(np.float64)
+    z = (polys[:, :h] + 1j * polys[:, h:]) * np.exp(1j * np.pi * np.arange(h) / N)
+    return np.fft.fft(z, axis=1) if negative_exponent else np.fft.ifft(z, axis=1) * h
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("convention", [0, 1])
+def test_upload_keys_fourier_natural_order(keyset, convention):
+    """fhs_upload_keys_fourier: a Fourier-domain BSK (what tfhe's ServerKey holds, src/lib.rs:64-72)
+    in natural frequency order, either exponent sign, gives the same decryptions through both
+    blind-rotation kernels (100 -> wide, 1024 -> throughput kernel) with f64-transform noise."""
+    import fhe_string_b200 as F
+    eng = F.Engine(0)
+    try:
+        eng.upload_keys_fourier(keyset.p, keyset.ksk(), _fourier_bsk(keyset, convention == 1),
+                                ksk_level_order=0, convention=convention)
+        tabs = bench_tables()
+        rng = np.random.default_rng(21 + convention)
+        for n in (100, 1024):
+            msgs = rng.integers(0, 16, n)
+            lut_id = (np.arange(n) % 8).astype(np.uint32)
+            out = eng.ks_pbs(keyset.encrypt(msgs, seed=77 + n), lut_id, tabs)
+            want = tabs[lut_id, msgs]
+            assert np.array_equal(keyset.decrypt(out), want), (convention, n)
+            assert float(np.std(keyset.phase_error(out, want))) < 3.2e-5
+    finally:
+        eng.close()
+
+
+@pytest.mark.gpu
+def test_upload_keys_fourier_convention_matters(keyset):
+    """The same spectra declared with the other exponent sign are a different (wrong) key."""
+    import fhe_string_b200 as F
+    eng = F.Engine(0)
+    try:
+        eng.upload_keys_fourier(keyset.p, keyset.ksk(), _fourier_bsk(keyset, False), convention=1)
+        tabs = bench_tables()
+        msgs = np.random.default_rng(5).integers(0, 16, 64)
+        lut_id = np.zeros(64, dtype=np.uint32)
+        out = eng.ks_pbs(keyset.encrypt(msgs, seed=5), lut_id, tabs)
+        assert not np.array_equal(keyset.decrypt(out), tabs[lut_id, msgs])
+        with pytest.raises(F.FhsError):
+            eng.upload_keys_fourier(keyset.p, keyset.ksk(), _fourier_bsk(keyset, False), convention=7)
+    finally:
+        eng.close()
