@@ -71,18 +71,35 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    # FHS_TORCH_ALLGATHER=1: A/B against the torch.distributed callback exchange
+    native_comm = os.environ.get("FHS_TORCH_ALLGATHER", "0") != "1"
     result = {"n_gpus": world, "unit": "ms wall-clock per call, max over ranks"}
+    if world > 1:
+        result["exchange"] = ("fhs_comm_allgather (ncclAllGather in place on the context's stream)" if native_comm
+                              else "torch.distributed.all_gather_into_tensor callback")
 
     def setup(l, seed):
         """keys for max length l: rank 0 generates, server keys broadcast over NCCL, uploaded per GPU."""
         ck = ClientKey(l=l, seed=seed) if rank == 0 else None
-        ksk = bcast_np(ck.ksk() if rank == 0 else None)
-        bsk = bcast_np(ck.bsk() if rank == 0 else None)
         nbu = [ck.num_blocks_usize] if rank == 0 else [None]
         if dist is not None:
             dist.broadcast_object_list(nbu, 0)
         eng = Engine(local)
-        eng.upload_keys(ck.p if rank == 0 else default_params(), ksk, bsk)
+        prm = ck.p if rank == 0 else default_params()
+        if world > 1 and native_comm:
+            # the library's own communicator: keys by fhs_comm_broadcast_host, levels by fhs_comm_allgather
+            eng.comm_init_from_torch()
+            big = prm.glwe_dim * prm.poly_size
+            shapes = (big * prm.ks_level * (prm.lwe_dim + 1), prm.lwe_dim * prm.pbs_level * (prm.glwe_dim + 1) ** 2 * prm.poly_size)
+            ksk, bsk = (np.ascontiguousarray(src(), dtype=np.uint64).reshape(-1).copy() if rank == 0
+                        else np.empty(n, dtype=np.uint64)
+                        for src, n in zip((ck.ksk, ck.bsk) if rank == 0 else (None, None), shapes))
+            eng.comm_broadcast(ksk)
+            eng.comm_broadcast(bsk)
+        else:
+            ksk = bcast_np(ck.ksk() if rank == 0 else None)
+            bsk = bcast_np(ck.bsk() if rank == 0 else None)
+        eng.upload_keys(prm, ksk, bsk)
         return ck, eng, nbu[0]
 
     def run_op(ck, eng, nbu, op, strs, pads, scalars=(), reps=2, want=None):

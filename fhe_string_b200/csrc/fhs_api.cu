@@ -148,6 +148,7 @@ void fhs_ctx_destroy(fhs_ctx *h) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    fhs::comm_release(c);
     fhs::free_keys(c);
     cudaFree(c->d_twiddle);
     cudaFree(c->d_small);

@@ -48,6 +48,9 @@ struct Ctx {
     int sm_count = 0;
     // cudaFuncSetAttribute is per device: done once per context, not once per process
     bool attr_br = false, attr_brw = false, attr_ks = false, attr_ksu = false;
+    // comm.cu: NCCL communicator of this rank (one process per GPU); null on single-GPU contexts
+    void *nccl_comm = nullptr;
+    int comm_rank = 0, comm_world = 1;
 };
 
 void set_error(const char *fmt, ...);
@@ -83,5 +86,7 @@ int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_
                              const uint64_t *d_tables, size_t batch, uint64_t *d_out);
 int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc);
 size_t bsk_fourier_elems(const Ctx *c);
+// comm.cu
+void comm_release(Ctx *c);
 
 }  // namespace fhs

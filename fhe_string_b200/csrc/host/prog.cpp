@@ -272,7 +272,12 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
                                     uint64_t *out_blocks, double stats[4], int rank, int world,
                                     size_t shard_min, fhs_allgather_fn allgather, void *user) {
     if (!p || !ctx || (!in_blocks && p->n_inputs) || !out_blocks) return FHS_ERR_INVALID;
-    if (world < 1 || rank < 0 || rank >= world || (world > 1 && !allgather)) return FHS_ERR_INVALID;
+    if (world < 1 || rank < 0 || rank >= world) return FHS_ERR_INVALID;
+    if (world > 1 && !allgather) {
+        // no callback: the context's own NCCL communicator (fhs_comm_init) must match rank / world
+        int cr = -1, cw = 0;
+        if (fhs_comm_info(ctx, &cr, &cw) != FHS_OK || cr != rank || cw != world) return FHS_ERR_COMM;
+    }
     if (shard_min == 0) shard_min = 148;
     const Graph &g = p->g;
     fhs_params prm;
@@ -354,8 +359,15 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
         for (const Grp &G : groups) {
             if (G.hi > G.lo && (rc = fhs_level_run(pool, G.row0 + G.lo, G.hi - G.lo, G.is_pbs ? 1 : 0, G.out_base + G.lo)) != FHS_OK) break;
             if (G.per) {  // exchange result blocks: rank q owns [out_base + q*per, out_base + (q+1)*per)
-                fhs_ctx_synchronize(ctx);
-                if (allgather(user, fhs_pool_device_ptr(pool) + G.out_base * width, G.per * width * sizeof(uint64_t)) != 0) { rc = FHS_ERR_COMM; break; }
+                uint64_t *base = fhs_pool_device_ptr(pool) + G.out_base * width;
+                const size_t bytes = G.per * width * sizeof(uint64_t);
+                if (!allgather) {
+                    // ncclAllGather in place, on the stream the level's kernels run on: no host sync
+                    if ((rc = fhs_comm_allgather(ctx, base, bytes)) != FHS_OK) break;
+                } else {
+                    fhs_ctx_synchronize(ctx);
+                    if (allgather(user, base, bytes) != 0) { rc = FHS_ERR_COMM; break; }
+                }
             }
         }
         if (rc != FHS_OK) break;

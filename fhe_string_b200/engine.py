@@ -30,6 +30,8 @@ FOURIER_NATURAL_NEG = 1
 EXPORTS = [
     "fhs_default_params", "fhs_last_error", "fhs_version", "fhs_ctx_create", "fhs_ctx_destroy",
     "fhs_ctx_set_stream", "fhs_ctx_synchronize", "fhs_upload_keys", "fhs_upload_keys_fourier", "fhs_ks_pbs_batch",
+    "fhs_comm_unique_id", "fhs_comm_init", "fhs_comm_info", "fhs_comm_destroy", "fhs_comm_allgather",
+    "fhs_comm_broadcast_host",
     "fhs_ks_pbs_batch_dev", "fhs_keyswitch_batch", "fhs_keyswitch_batch_dev", "fhs_build_lut",
     "fhs_pbs_batch", "fhs_pbs_batch_dev", "fhs_last_kernel_ms", "fhs_launch_count",
     "fhs_measure_fp64_tflops",
@@ -64,6 +66,13 @@ def load_library():
     L.fhs_ctx_synchronize.argtypes = [vp]
     L.fhs_upload_keys.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, vp]
     L.fhs_upload_keys_fourier.argtypes = [vp, ctypes.POINTER(Params), vp, ctypes.c_int, vp, ctypes.c_int]
+    L.fhs_comm_unique_id.argtypes = [vp]
+    L.fhs_comm_init.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int]
+    L.fhs_comm_info.argtypes = [vp, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int)]
+    L.fhs_comm_destroy.argtypes = [vp]
+    L.fhs_comm_destroy.restype = None
+    L.fhs_comm_allgather.argtypes = [vp, vp, ctypes.c_size_t]
+    L.fhs_comm_broadcast_host.argtypes = [vp, vp, ctypes.c_size_t, ctypes.c_int]
     L.fhs_ks_pbs_batch.argtypes = [vp, vp, vp, vp, sz, sz, vp]
     L.fhs_ks_pbs_batch_dev.argtypes = [vp, vp, vp, vp, sz, sz, vp]
     L.fhs_keyswitch_batch.argtypes = [vp, vp, sz, vp]
@@ -101,6 +110,7 @@ class Engine:
         self.h = h
         self.device = device
         self.p = None
+        self.comm = None   # (rank, world) once comm_init has run
 
     def _check(self, rc):
         if rc != 0:
@@ -143,6 +153,39 @@ class Engine:
         self._check(self.L.fhs_upload_keys_fourier(self.h, ctypes.byref(p), kp, int(ksk_level_order),
                                                    bf.ctypes.data_as(ctypes.c_void_p), int(convention)))
         self._keys_uploaded(p, big)
+
+    # ---- multi-GPU (one process per GPU): the library's own NCCL communicator ----
+    def comm_unique_id(self):
+        """fhs_comm_unique_id: 128 bytes made on one rank, to be shipped to the others."""
+        buf = (ctypes.c_uint8 * 128)()
+        self._check(self.L.fhs_comm_unique_id(buf))
+        return bytes(buf)
+
+    def comm_init(self, unique_id, rank, world):
+        buf = (ctypes.c_uint8 * 128).from_buffer_copy(unique_id)
+        self._check(self.L.fhs_comm_init(self.h, buf, int(rank), int(world)))
+        self.comm = (int(rank), int(world))
+
+    def comm_init_from_torch(self):
+        """Bootstrap over an initialised torch.distributed group: rank 0's id is broadcast as an object."""
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+        box = [self.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, 0)
+        self.comm_init(box[0], rank, world)
+
+    def comm_broadcast(self, arr, root=0):
+        """fhs_comm_broadcast_host on a numpy array that has the same shape/dtype on every rank (in place)."""
+        assert arr.flags["C_CONTIGUOUS"] and arr.flags["WRITEABLE"]
+        self._check(self.L.fhs_comm_broadcast_host(self.h, arr.ctypes.data_as(ctypes.c_void_p), arr.nbytes, int(root)))
+        return arr
+
+    def comm_allgather_dev(self, dev_ptr, bytes_per_rank):
+        self._check(self.L.fhs_comm_allgather(self.h, ctypes.c_void_p(dev_ptr), int(bytes_per_rank)))
+
+    def comm_destroy(self):
+        self.L.fhs_comm_destroy(self.h)
+        self.comm = None
 
     def _keys_uploaded(self, p, big):
         self.p = p

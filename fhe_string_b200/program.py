@@ -117,8 +117,18 @@ class Program:
 
     def run_sharded(self, engine, in_blocks, rank, world, shard_min=148):
         """One process per GPU; every rank passes the same inputs.  Levels are split by rank and
-        re-assembled with torch.distributed.all_gather_into_tensor (NCCL over NVLink) in place on
-        the device pool."""
+        re-assembled in place on the device pool: by the library's own ncclAllGather on the context's
+        stream when the engine has a communicator (Engine.comm_init*; no host synchronisation between
+        levels), else through a torch.distributed.all_gather_into_tensor callback."""
+        inb = np.ascontiguousarray(in_blocks, dtype=np.uint64).reshape(self.n_inputs, -1)
+        out = np.empty((self.n_outputs, inb.shape[1] if self.n_inputs else engine.big), dtype=np.uint64)
+        stats = np.zeros(4, dtype=np.float64)
+        if getattr(engine, "comm", None) == (rank, world):
+            rc = self.L.fhs_prog_run_sharded(self.h, engine.h, inb.ctypes.data, out.ctypes.data, stats.ctypes.data,
+                                             rank, world, shard_min, None, None)
+            if rc != 0:
+                raise FhsError(f"fhs_prog_run_sharded({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()}")
+            return out, dict(levels=int(stats[0]), pbs=int(stats[1]), launches=int(stats[2]), ms=float(stats[3]))
         import torch
         import torch.distributed as dist
 
@@ -139,9 +149,6 @@ class Program:
 
         cb_t = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
         cb = cb_t(_allgather)
-        inb = np.ascontiguousarray(in_blocks, dtype=np.uint64).reshape(self.n_inputs, -1)
-        out = np.empty((self.n_outputs, inb.shape[1] if self.n_inputs else engine.big), dtype=np.uint64)
-        stats = np.zeros(4, dtype=np.float64)
         rc = self.L.fhs_prog_run_sharded(self.h, engine.h, inb.ctypes.data, out.ctypes.data, stats.ctypes.data,
                                          rank, world, shard_min, ctypes.cast(cb, ctypes.c_void_p), None)
         if rc != 0:

@@ -172,6 +172,27 @@ int fhs_pool_load_program(fhs_pool *pool, size_t rows, size_t terms, const uint3
                           size_t max_level_rows);
 int fhs_level_run(fhs_pool *pool, size_t row_lo, size_t B, int is_pbs, size_t out_slot);
 
+/* ---- multi-GPU: one process per GPU, a key replica per GPU ---------------------
+ * The path shards over independent LUT evaluations; the only traffic is the server keys once
+ * (broadcast) and the result blocks of a level that was split by rank (all-gather).  Both are NCCL
+ * collectives over NVLink enqueued on the context's stream.  NCCL is resolved with dlopen at the
+ * first call (the copy already loaded in the process, e.g. torch's, else the system libnccl.so.2;
+ * FHS_NCCL_LIB overrides); single-GPU callers never need it.
+ * Bootstrap: rank 0 calls fhs_comm_unique_id and ships the 128 bytes to the other ranks by any
+ * means (file, socket, MPI, torch.distributed); every rank then calls fhs_comm_init. */
+#define FHS_COMM_ID_BYTES 128
+int fhs_comm_unique_id(uint8_t id[FHS_COMM_ID_BYTES]);
+int fhs_comm_init(fhs_ctx *ctx, const uint8_t id[FHS_COMM_ID_BYTES], int rank, int world);
+int fhs_comm_info(fhs_ctx *ctx, int *rank, int *world);   /* FHS_ERR_COMM when there is none */
+void fhs_comm_destroy(fhs_ctx *ctx);
+/* In-place all-gather on device memory, asynchronous on the context's stream: rank q has written
+ * [d_base + q*bytes_per_rank, +bytes_per_rank); afterwards all world*bytes_per_rank bytes are equal
+ * on every rank.  Used by fhs_prog_run_sharded after every level that was split by rank. */
+int fhs_comm_allgather(fhs_ctx *ctx, uint64_t *d_base, size_t bytes_per_rank);
+/* Broadcast of a HOST buffer from `root` (staged through device memory, synchronous): how the
+ * server keys made on rank 0 reach the other ranks before each calls fhs_upload_keys. */
+int fhs_comm_broadcast_host(fhs_ctx *ctx, void *host_buf, size_t bytes, int root);
+
 #ifdef __cplusplus
 }
 #endif

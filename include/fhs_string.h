@@ -72,7 +72,11 @@ int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_instances, const
  * contiguously by rank; after such a level `allgather(user, device_base, bytes_per_rank)` must make
  * the world * bytes_per_rank bytes at device_base identical on all ranks (rank q contributes chunk q
  * in place: ncclAllGather / torch.distributed.all_gather_into_tensor).  Smaller levels are
- * replicated.  fhs_prog_plan reports, per level, {B, blocks per rank (0 = replicated), lo, hi}. */
+ * replicated.  fhs_prog_plan reports, per level, {B, blocks per rank (0 = replicated), lo, hi}.
+ * allgather == NULL selects the library's own exchange: ncclAllGather in place on the context's
+ * stream through the communicator set up with fhs_comm_init (fhs_cuda.h) -- no host
+ * synchronisation between levels, no host framework in the loop; FHS_ERR_COMM if the context has no
+ * communicator of this rank / world. */
 typedef int (*fhs_allgather_fn)(void *user, uint64_t *device_base, size_t bytes_per_rank);
 int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks, uint64_t *out_blocks,
                          double stats[4], int rank, int world, size_t shard_min,
