@@ -11,7 +11,7 @@
 #include <dlfcn.h>
 
 #include <cstring>
-#include <vector>
+#include <mutex>
 
 #include "fhs_internal.cuh"
 
@@ -36,8 +36,14 @@ struct NcclApi {
 };
 NcclApi g_nccl;
 
+std::mutex g_nccl_mu;   // contexts of different threads may initialise their communicators concurrently
+
 bool load_nccl() {
-    if (g_nccl.tried) return g_nccl.ok;
+    std::lock_guard<std::mutex> lock(g_nccl_mu);
+    if (g_nccl.tried) {
+        if (!g_nccl.ok) set_error("NCCL unavailable (earlier dlopen / dlsym failure); set FHS_NCCL_LIB");
+        return g_nccl.ok;
+    }
     g_nccl.tried = true;
     const char *names[] = {getenv("FHS_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
     for (const char *n : names) {
