@@ -44,3 +44,27 @@ def test_cmd_driver_all_equal():
                         "--pattern", "bc", "--seed", "3"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "❌" not in r.stdout and "all equal: True" in r.stdout
+
+
+def test_config4_256_char_ops_full_size():
+    """BASELINE configs[3] at full size: keys for l = 256 (5 usize blocks), a 200-char string of words
+    padded to 256 (257 FheAsciiChar = 1 028 blocks); split(" "), replace(2-char pattern, "c", l=256),
+    to_uppercase / to_lowercase decrypt to the Python str answers; round trip and idempotence hold."""
+    import numpy as np
+    from fhe_string_b200.api import generate_keys
+    ck, sk = generate_keys(l=256, seed=5)
+    assert ck.num_blocks_usize == 5
+    rng = np.random.default_rng(11)
+    words = ["".join(chr(int(c)) for c in rng.integers(97, 123, rng.integers(2, 7))) for _ in range(80)]
+    s = " ".join(words)[:200]
+    es = ck.encrypt_str(s, 256)
+    assert es.decrypt(ck) == s
+    up = es.to_uppercase(sk)
+    assert up.decrypt(ck) == s.upper()
+    assert up.to_uppercase(sk).decrypt(ck) == s.upper()              # idempotent
+    assert up.to_lowercase(sk).decrypt(ck) == s                      # round trip (input is lowercase)
+    assert es.split(sk, ck.encrypt_str(" ")).decrypt(ck) == s.split(" ")
+    pat = s[50:52]
+    assert es.replace(sk, ck.encrypt_str(pat), ck.encrypt_str("c"), 256).decrypt(ck) == s.replace(pat, "c")
+    assert es.len(sk).decrypt(ck) == 200
+    sk.engine.close()
