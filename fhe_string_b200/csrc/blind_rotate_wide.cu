@@ -441,6 +441,15 @@ int w_ilog2(uint32_t x) {
 int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
                              const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
+    {   // smallest levels: one ciphertext per pair of SMs (FHS_BR_PAIR=0 disables)
+        static int pair_on = -1;
+        if (pair_on < 0) {
+            const char *e = getenv("FHS_BR_PAIR");
+            pair_on = e ? atoi(e) : 1;
+        }
+        if (pair_on && (long)batch <= (long)blind_rotate_pair_limit(c))
+            return launch_blind_rotate_pair(c, d_small, d_lut_id, d_tables, batch, d_out);
+    }
     if (!c->attr_brw) {
         FHS_CUDA(cudaFuncSetAttribute(blind_rotate_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)kWSmemBytes));

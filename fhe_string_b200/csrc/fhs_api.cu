@@ -63,8 +63,9 @@ static void free_keys(Ctx *c) {
     c->d_ksk_t = c->d_ksk_u = nullptr;
     cudaFree(c->d_bsk_f);
     cudaFree(c->d_bsk_w);
+    cudaFree(c->d_bsk_x);
     c->d_ksk = c->d_ksk_corr = nullptr;
-    c->d_bsk_f = c->d_bsk_w = nullptr;
+    c->d_bsk_f = c->d_bsk_w = c->d_bsk_x = nullptr;
     c->has_keys = false;
 }
 
@@ -247,7 +248,8 @@ static int upload_keys_impl(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk
             (e = cudaMalloc(&c->d_ksk_t, fhs::ksk_tiles_bytes(c))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_ksk_u, fhs::ksk_umma_tiles_bytes(c))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_bsk_f, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess ||
-            (e = cudaMalloc(&c->d_bsk_w, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess) {
+            (e = cudaMalloc(&c->d_bsk_w, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess ||
+            (e = cudaMalloc(&c->d_bsk_x, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "cudaMalloc(keys)");
             break;
         }
@@ -281,6 +283,7 @@ static int upload_keys_impl(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk
             if ((rc = f64_only ? fhs::launch_bsk_transform(c, d_raw) : fhs::launch_bsk_transform_dd(c, d_raw)) != FHS_OK)
                 break;
         }
+        if ((rc = fhs::launch_bsk_pair_repack(c)) != FHS_OK) break;
         if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "bsk transform");
             break;

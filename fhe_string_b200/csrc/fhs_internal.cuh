@@ -31,6 +31,8 @@ struct Ctx {
     uint64_t *d_ksk_corr = nullptr;// [n+1]  2^(base_log-1) * sum of all KSK rows (unsigned-digit offset)
     double2 *d_bsk_f = nullptr;    // Fourier BSK, layout in blind_rotate.cu
     double2 *d_bsk_w = nullptr;    // the same values in the layout of blind_rotate_wide.cu
+    double2 *d_bsk_x = nullptr;    // ... and in the layout of blind_rotate_pair.cu (one GGSW row per CTA of a pair)
+    int pair_limit = -1;           // largest batch of the pair kernel on this device (-1: not queried yet)
     double2 *d_twiddle = nullptr;  // [32][33] inter-pass twiddles T[k2][n1]
     // scratch
     uint64_t *d_small = nullptr;   // [cap][n+1] keyswitched ciphertexts
@@ -86,6 +88,11 @@ int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_
                              const uint64_t *d_tables, size_t batch, uint64_t *d_out);
 int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc);
 size_t bsk_fourier_elems(const Ctx *c);
+// blind_rotate_pair.cu: one ciphertext per 2-CTA cluster, for levels of at most one ciphertext per two SMs
+int launch_bsk_pair_repack(Ctx *c);
+int blind_rotate_pair_limit(Ctx *c);
+int launch_blind_rotate_pair(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
+                             const uint64_t *d_tables, size_t batch, uint64_t *d_out);
 // comm.cu
 void comm_release(Ctx *c);
 
