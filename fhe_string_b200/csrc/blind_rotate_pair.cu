@@ -8,8 +8,8 @@
 // CTA p of the pair owns accumulator polynomial p (0 = mask, 1 = body) end to end:
 //   decomposition of (X^a - 1) acc_p, forward FFT, both products of the GGSW row p
 //       keep_p[k] = D_p[k] B[p][p][k]        send_p[k] = D_p[k] B[p][1-p][k],
-//   send_p goes straight into the PEER's shared memory (st.shared::cluster), completion is signalled
-//   on the peer's mbarrier (mbarrier.arrive.release.cluster), out_p = keep_p + recv, inverse FFT,
+//   send_p goes straight into the PEER's shared memory with st.async, whose bytes complete a
+//   transaction on the peer's mbarrier (no fence, no remote arrive), out_p = keep_p + recv, inverse FFT,
 //   torus accumulation.  One 16 KB exchange per direction and iteration, no cluster-wide barrier in
 //   the loop; receive buffers and mbarriers are double-buffered so the peer may run one iteration ahead.
 //
@@ -65,21 +65,25 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
     return r;
 }
-__device__ __forceinline__ void st_peer_f64x2(uint32_t caddr, double x, double y) {
-    asm volatile("st.shared::cluster.v2.f64 [%0], {%1, %2};" ::"r"(caddr), "d"(x), "d"(y) : "memory");
+// 16-byte store into the peer's shared memory that reports its bytes to the peer's mbarrier when it
+// has landed: no release fence on the sender (an mbarrier.arrive.release.cluster after plain remote
+// stores compiles to MEMBAR.ALL.GPU + ERRBAR and cost 40 % of an iteration)
+__device__ __forceinline__ void st_peer_f64x2(uint32_t caddr, double x, double y, uint32_t cmbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];"
+                 ::"r"(caddr), "d"(x), "d"(y), "r"(cmbar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t saddr, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(saddr), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_init(uint32_t saddr, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(saddr), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_peer(uint32_t caddr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(caddr) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t saddr, uint32_t parity) {
     uint32_t ok;
     do {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(ok) : "r"(saddr), "r"(parity) : "memory");
     } while (!ok);
@@ -150,8 +154,8 @@ blind_rotate_pair_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
     const uint32_t mbar0 = (uint32_t)__cvta_generic_to_shared(&sm.mbar[0]);
     if (warp == 0) tmem_alloc(&sm.tmem_base, kPTmemCols);
     if (threadIdx.x == 32) {
-        mbar_init(mbar0, 128);
-        mbar_init(mbar0 + 8, 128);
+        mbar_init(mbar0, 1);                                       // one local arrival (expect_tx) + 16 KB of peer stores
+        mbar_init(mbar0 + 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     tmem_fence_before_sync();
@@ -322,6 +326,7 @@ blind_rotate_pair_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
             // ---- GGSW row p against the BSK slice parked in TMEM; "send" products go to the peer ----
             pbar_sync(kPBarFull, kPThreads);
             tmem_fence_after_sync();
+            if (t == 0) mbar_expect_tx(mbar0 + 8u * (uint32_t)buf, 8u * 128u * (uint32_t)sizeof(double2));
             {
                 uint32_t br0[32], br1[32];
                 tmem_ld32(tbsk, br0);
@@ -335,7 +340,7 @@ blind_rotate_pair_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                         const double cky = p_dbl(br[8 * k + 6], br[8 * k + 7]);
                         const double dr = xr[m], di = xi[m];
                         st_peer_f64x2(peer_recv + (uint32_t)((buf * 8 + m) * 128 * sizeof(double2)),
-                                      dr * csx - di * csy, dr * csy + di * csx);
+                                      dr * csx - di * csy, dr * csy + di * csx, peer_mbar + 8u * (uint32_t)buf);
                         xr[m] = dr * ckx - di * cky;
                         xi[m] = dr * cky + di * ckx;
                     }
@@ -350,7 +355,6 @@ blind_rotate_pair_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
                 tmem_fence_before_sync();
                 pbar_arrive(kPBarFree, kPThreads);
             }
-            mbar_arrive_peer(peer_mbar + 8u * (uint32_t)buf);      // releases the 8 remote stores above
             mbar_wait(mbar0 + 8u * (uint32_t)buf, (uint32_t)(i >> 1) & 1u);
 #pragma unroll
             for (int m = 0; m < 8; m++) {
