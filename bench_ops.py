@@ -3,7 +3,7 @@
 
   config 3: eq / contains / find on a 64-char padded string, 8-char pattern           (1 GPU)
   config 4: split / replace / to_uppercase on a 256-char padded string (l=256, U=5)    (N GPUs,
-            levels of >= 148*N LUT evaluations split by rank, all-gather of result blocks)
+            levels of more than 74 LUT evaluations split by rank, all-gather of result blocks)
   config 5: 1024 independent comparisons (lt, eq) of 64-char padded strings, instances sharded
             over the ranks with no exchange (fhs_prog_run_many)
 

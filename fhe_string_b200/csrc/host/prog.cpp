@@ -232,11 +232,11 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
 // Executor: level by level on a device-resident pool (fhs_pool / fhs_level of include/fhs_cuda.h).
 #include <chrono>
 
-// Slice of a level of B evaluations owned by `rank`.  A level of at most shard_min evaluations (148 =
-// one wave of the wide blind-rotation kernel, 2.3 ms however few ciphertexts it has) is computed
+// Slice of a level of B evaluations owned by `rank`.  A level of at most shard_min evaluations (74 =
+// one wave of the pair blind-rotation kernel, 1.7 ms however few ciphertexts it has) is computed
 // redundantly by every rank; anything larger is split, because ceil(B / world) ciphertexts per GPU
-// finish sooner than B on one GPU even after the all-gather (B = 592: 6.2 ms on one GPU, 2.3 ms +
-// exchange on four).
+// finish sooner than B on one GPU even after the all-gather (B = 148: 2.3 ms on one GPU, 1.7 ms +
+// exchange on two; B = 592: 6.2 ms on one GPU, 1.7 ms + exchange on eight).
 static void level_slice(size_t B, int rank, int world, size_t shard_min, size_t *per, size_t *lo, size_t *hi) {
     if (world <= 1 || B <= shard_min) { *per = 0; *lo = 0; *hi = B; return; }
     *per = (B + world - 1) / world;
@@ -278,7 +278,7 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
         int cr = -1, cw = 0;
         if (fhs_comm_info(ctx, &cr, &cw) != FHS_OK || cr != rank || cw != world) return FHS_ERR_COMM;
     }
-    if (shard_min == 0) shard_min = 148;
+    if (shard_min == 0) shard_min = 74;
     const Graph &g = p->g;
     fhs_params prm;
     int rc = fhs_ctx_get_params(ctx, &prm);
@@ -417,8 +417,8 @@ extern "C" int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_insta
     for (auto &v : pbs_at) gmax = std::max(gmax, v.size());
     // Chunk size: at most kManyChunk evaluations in the largest level, and among those sizes the one
     // that minimises (number of chunks) x (blind-rotation rounds per chunk).  A round is 4 ciphertexts
-    // per SM (592 on a B200); a remainder of <= 148 / <= 296 goes to the wide kernel at 0.39 / 0.59 of
-    // a round.  A short last chunk still runs whole levels, so equal chunks beat "full chunks + a rest".
+    // per SM (592 on a B200); a remainder of <= 74 goes to the pair kernel (0.28 of a round), of
+    // <= 148 / <= 296 to the wide kernel (0.39 / 0.59).  A short last chunk still runs whole levels, so equal chunks beat "full chunks + a rest".
     const size_t Mc_max = std::max<size_t>(1, std::min(M, kManyChunk / gmax));
     size_t Mc = Mc_max;
     {
@@ -429,7 +429,7 @@ extern "C" int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_insta
             for (auto &v : pbs_at) {
                 if (v.empty()) continue;
                 const size_t rows = v.size() * cand, rem = rows % kRound;
-                rounds += (double)(rows / kRound) + (rem == 0 ? 0.0 : rem <= 148 ? 0.39 : rem <= 296 ? 0.59 : 1.0);
+                rounds += (double)(rows / kRound) + (rem == 0 ? 0.0 : rem <= 74 ? 0.28 : rem <= 148 ? 0.39 : rem <= 296 ? 0.59 : 1.0);
             }
             const double cost = rounds * (double)((M + cand - 1) / cand);
             if (best < 0.0 || cost < best) { best = cost; Mc = cand; }

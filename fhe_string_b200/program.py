@@ -106,7 +106,7 @@ class Program:
             raise FhsError(f"fhs_prog_run_many({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()}")
         return out, dict(levels=int(stats[0]), pbs=int(stats[1]), launches=int(stats[2]), ms=float(stats[3]))
 
-    def plan(self, rank, world, shard_min=148):
+    def plan(self, rank, world, shard_min=74):
         """Per level: (B, blocks per rank or 0 if replicated, lo, hi) for `rank` of `world`."""
         n = ctypes.c_size_t()
         buf = np.zeros(4 * max(self.depth, 1), dtype=np.uint64)
@@ -115,7 +115,7 @@ class Program:
             raise FhsError("fhs_prog_plan failed")
         return buf[: 4 * n.value].reshape(-1, 4)
 
-    def run_sharded(self, engine, in_blocks, rank, world, shard_min=148):
+    def run_sharded(self, engine, in_blocks, rank, world, shard_min=74):
         """One process per GPU; every rank passes the same inputs.  Levels are split by rank and
         re-assembled in place on the device pool: by the library's own ncclAllGather on the context's
         stream when the engine has a communicator (Engine.comm_init*; no host synchronisation between

@@ -68,7 +68,7 @@ int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_instances, const
                       uint64_t *out_blocks, double stats[4]);
 
 /* Multi-GPU (one process per GPU, every rank holds a key replica and runs the same program on the
- * same inputs): levels with more than shard_min evaluations (0 = default 148, one blind-rotation wave) are split
+ * same inputs): levels with more than shard_min evaluations (0 = default 74, one wave of the pair blind-rotation kernel) are split
  * contiguously by rank; after such a level `allgather(user, device_base, bytes_per_rank)` must make
  * the world * bytes_per_rank bytes at device_base identical on all ranks (rank q contributes chunk q
  * in place: ncclAllGather / torch.distributed.all_gather_into_tensor).  Smaller levels are

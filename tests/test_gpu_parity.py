@@ -291,3 +291,49 @@ def test_upload_keys_fourier_convention_matters(keyset):
             eng.upload_keys_fourier(keyset.p, keyset.ksk(), _fourier_bsk(keyset, False), convention=7)
     finally:
         eng.close()
+
+
+_PAIR_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+import fhe_string_b200 as F
+from oracle import oracle as O
+from conftest import bench_tables
+ks = O.Keyset(seed=1)
+eng = F.Engine(0)
+eng.upload_keys(ks.p, ks.ksk(), ks.bsk(), ksk_level_order=0)
+tabs = bench_tables()
+outs = []
+for n in (1, 2, 37, 74):
+    msgs = np.random.default_rng(100 + n).integers(0, 16, n)
+    lut_id = (np.arange(n) % 8).astype(np.uint32)
+    out = eng.ks_pbs(ks.encrypt(msgs, seed=300 + n), lut_id, tabs)
+    want = tabs[lut_id, msgs]
+    assert np.array_equal(ks.decrypt(out), want), n
+    assert float(np.std(ks.phase_error(out, want))) < 4e-5
+    outs.append(out)
+np.save(sys.argv[2], np.concatenate(outs))
+print("pair ok", eng.launch_count())
+"""
+
+
+@pytest.mark.gpu
+def test_pair_kernel_against_wide_kernel(tmp_path):
+    """Levels of <= 74 evaluations run on blind_rotate_pair_kernel (one ciphertext per 2-CTA cluster,
+    cross terms over distributed shared memory); FHS_BR_PAIR=0 sends the same batches to the wide
+    kernel.  Same decryptions, and the two output ciphertexts differ only by FFT rounding (different
+    FFT factorisation): every body and mask coefficient within 2^-24 of the torus."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    files = {}
+    for flag in ("1", "0"):
+        files[flag] = str(tmp_path / f"out{flag}.npy")
+        env = dict(os.environ, FHS_BR_PAIR=flag)
+        r = subprocess.run([sys.executable, "-c", _PAIR_SCRIPT, root, files[flag]], env=env, capture_output=True,
+                           text=True, timeout=600)
+        assert r.returncode == 0 and "pair ok" in r.stdout, r.stderr[-2000:]
+    a, b = np.load(files["1"]), np.load(files["0"])
+    diff = (a - b).view(np.int64).astype(np.float64) / 2.0 ** 64
+    assert not np.array_equal(a, b)              # really two different kernels
+    assert float(np.abs(diff).max()) < 2.0 ** -24
