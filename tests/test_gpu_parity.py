@@ -303,16 +303,15 @@ ks = O.Keyset(seed=1)
 eng = F.Engine(0)
 eng.upload_keys(ks.p, ks.ksk(), ks.bsk(), ksk_level_order=0)
 tabs = bench_tables()
-outs = []
+errs = []
 for n in (1, 2, 37, 74):
     msgs = np.random.default_rng(100 + n).integers(0, 16, n)
     lut_id = (np.arange(n) % 8).astype(np.uint32)
     out = eng.ks_pbs(ks.encrypt(msgs, seed=300 + n), lut_id, tabs)
     want = tabs[lut_id, msgs]
     assert np.array_equal(ks.decrypt(out), want), n
-    assert float(np.std(ks.phase_error(out, want))) < 4e-5
-    outs.append(out)
-np.save(sys.argv[2], np.concatenate(outs))
+    errs.append(ks.phase_error(out, want))
+np.save(sys.argv[2], np.concatenate(errs))
 print("pair ok", eng.launch_count())
 """
 
@@ -321,19 +320,21 @@ print("pair ok", eng.launch_count())
 def test_pair_kernel_against_wide_kernel(tmp_path):
     """Levels of <= 74 evaluations run on blind_rotate_pair_kernel (one ciphertext per 2-CTA cluster,
     cross terms over distributed shared memory); FHS_BR_PAIR=0 sends the same batches to the wide
-    kernel.  Same decryptions, and the two output ciphertexts differ only by FFT rounding (different
-    FFT factorisation): every body and mask coefficient within 2^-24 of the torus."""
+    kernel.  Same decryptions and the same noise level.  (The ciphertexts themselves are NOT comparable
+    coefficient by coefficient: one digit that rounds the other way adds a whole GGSW row, a different
+    but equally valid encryption -- which is why this tier is noise-bounded, not bit-exact.)"""
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    files = {}
+    err = {}
     for flag in ("1", "0"):
-        files[flag] = str(tmp_path / f"out{flag}.npy")
+        f = str(tmp_path / f"err{flag}.npy")
         env = dict(os.environ, FHS_BR_PAIR=flag)
-        r = subprocess.run([sys.executable, "-c", _PAIR_SCRIPT, root, files[flag]], env=env, capture_output=True,
+        r = subprocess.run([sys.executable, "-c", _PAIR_SCRIPT, root, f], env=env, capture_output=True,
                            text=True, timeout=600)
         assert r.returncode == 0 and "pair ok" in r.stdout, r.stderr[-2000:]
-    a, b = np.load(files["1"]), np.load(files["0"])
-    diff = (a - b).view(np.int64).astype(np.float64) / 2.0 ** 64
-    assert not np.array_equal(a, b)              # really two different kernels
-    assert float(np.abs(diff).max()) < 2.0 ** -24
+        err[flag] = np.load(f)
+    assert not np.array_equal(err["1"], err["0"])            # really two different kernels
+    s1, s0 = float(np.std(err["1"])), float(np.std(err["0"]))
+    assert s1 < 4e-5 and s0 < 4e-5 and abs(s1 - s0) < 1e-5, (s1, s0)
+    assert float(np.abs(err["1"]).max()) < 2.0 ** -11 and float(np.abs(err["1"] - err["0"]).max()) < 2.0 ** -10
