@@ -59,3 +59,20 @@ def test_level_plan_two_ranks_gloo():
         assert pr.exitcode == 0
     assert ok and n_levels == depth
     assert sharded >= 2   # the big first levels of contains(65 x 9) are split, the reductions are not
+
+
+def test_default_shard_threshold_is_one_pair_wave():
+    """Levels above 74 evaluations (one wave of the pair blind-rotation kernel) are split by rank; at or
+    below it they are replicated.  eq(65 x 65) has levels [130, 9, 1]: on 8 ranks the first one becomes
+    17 per rank, the reductions stay whole."""
+    sys.path.insert(0, ROOT)
+    from fhe_string_b200.program import Program
+    p = Program("eq", [65, 65])
+    plans = [p.plan(r, 8).astype(np.int64) for r in range(8)]
+    assert [int(x) for x in plans[0][:, 0]] == [130, 9, 1]
+    assert int(plans[0][0, 1]) == 17 and all(int(pl[1, 1]) == 0 and int(pl[2, 1]) == 0 for pl in plans)
+    covered = sorted((int(pl[0, 2]), int(pl[0, 3])) for pl in plans)
+    assert covered[0][0] == 0 and covered[-1][1] == 130
+    assert all(covered[i][1] == covered[i + 1][0] for i in range(7))
+    one = Program("contains", [65, 9]).plan(0, 1)
+    assert all(int(x) == 0 for x in one[:, 1])           # a single rank never splits

@@ -3,6 +3,7 @@
 #   main : GPU tests, smoke, bench (+ reference arm), op benches, then the ncu launch list of the bench command
 #   full : ncu --set full of the hot kernels of one bench step (digit prologue, tcgen05 keyswitch, blind rotation)
 #   wide : ncu --set full of the small-level (wide) blind-rotation kernel at 148 ciphertexts
+#   pair : ncu --set full of the 2-CTA-cluster (pair) blind-rotation kernel at 74 ciphertexts
 set -x
 MODE=${1:-main}
 mkdir -p gpurun_out
@@ -27,4 +28,7 @@ elif [ "$MODE" = full ]; then
 elif [ "$MODE" = wide ]; then
   timeout 300 python scratch/dev_br.py 148 > gpurun_out/plain_w.log 2>&1 &&
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:blind_rotate_wide -s 1 -c 1 -f -o gpurun_out/prof_wide python scratch/dev_br.py 148 > gpurun_out/ncu_wide.log 2>&1
+elif [ "$MODE" = pair ]; then
+  timeout 300 python scratch/dev_br.py 74 > gpurun_out/plain_p.log 2>&1 &&
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:blind_rotate_pair -s 1 -c 1 -f -o gpurun_out/prof_pair python scratch/dev_br.py 74 > gpurun_out/ncu_pair.log 2>&1
 fi
