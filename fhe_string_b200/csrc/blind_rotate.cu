@@ -684,6 +684,20 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
             return launch_blind_rotate_wide(c, d_small + head * ((size_t)c->n + 1), d_lut_id + head, d_tables, rem,
                                             d_out + head * ((size_t)c->big + 1));
         }
+        // a remainder of up to one pair wave above two ciphertexts per SM: wide (3.6 ms) + pair (1.7 ms)
+        // instead of one more 4-slot round (5.9 ms)
+        const long pair_cap = blind_rotate_pair_limit(c);
+        if (wide_limit == 2L * c->sm_count && pair_cap > 0 && (long)rem > wide_limit && (long)rem <= wide_limit + pair_cap) {
+            const size_t head = batch - rem, mid = (size_t)wide_limit;
+            int rc = head ? launch_blind_rotate(c, d_small, d_lut_id, d_tables, head, d_out) : FHS_OK;
+            if (rc != FHS_OK) return rc;
+            rc = launch_blind_rotate_wide(c, d_small + head * ((size_t)c->n + 1), d_lut_id + head, d_tables, mid,
+                                          d_out + head * ((size_t)c->big + 1));
+            if (rc != FHS_OK) return rc;
+            const size_t h2 = head + mid;
+            return launch_blind_rotate_wide(c, d_small + h2 * ((size_t)c->n + 1), d_lut_id + h2, d_tables, rem - mid,
+                                            d_out + h2 * ((size_t)c->big + 1));
+        }
     }
     static bool knobs_read = false;
     static int stagger = 4, opt = 13;  // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1 | 5 | 13)

@@ -418,7 +418,7 @@ extern "C" int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_insta
     // Chunk size: at most kManyChunk evaluations in the largest level, and among those sizes the one
     // that minimises (number of chunks) x (blind-rotation rounds per chunk).  A round is 4 ciphertexts
     // per SM (592 on a B200); a remainder of <= 74 goes to the pair kernel (0.28 of a round), of
-    // <= 148 / <= 296 to the wide kernel (0.39 / 0.59).  A short last chunk still runs whole levels, so equal chunks beat "full chunks + a rest".
+    // <= 148 / <= 296 to the wide kernel (0.39 / 0.59), of <= 370 to wide + pair (0.89).  A short last chunk still runs whole levels, so equal chunks beat "full chunks + a rest".
     const size_t Mc_max = std::max<size_t>(1, std::min(M, kManyChunk / gmax));
     size_t Mc = Mc_max;
     {
@@ -429,7 +429,7 @@ extern "C" int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_insta
             for (auto &v : pbs_at) {
                 if (v.empty()) continue;
                 const size_t rows = v.size() * cand, rem = rows % kRound;
-                rounds += (double)(rows / kRound) + (rem == 0 ? 0.0 : rem <= 74 ? 0.28 : rem <= 148 ? 0.39 : rem <= 296 ? 0.59 : 1.0);
+                rounds += (double)(rows / kRound) + (rem == 0 ? 0.0 : rem <= 74 ? 0.28 : rem <= 148 ? 0.39 : rem <= 296 ? 0.59 : rem <= 370 ? 0.89 : 1.0);
             }
             const double cost = rounds * (double)((M + cand - 1) / cand);
             if (best < 0.0 || cost < best) { best = cost; Mc = cand; }
