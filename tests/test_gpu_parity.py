@@ -95,6 +95,21 @@ def test_ks_pbs_pipelined_host_call(engine, keyset, n):
     assert np.array_equal(keyset.decrypt(out), tables[lut_id, msgs])
 
 
+@pytest.mark.parametrize("n", [74, 75, 149, 297, 340, 370, 371, 621, 666, 962])
+def test_blind_rotation_dispatch_boundaries(engine, keyset, n):
+    """launch_blind_rotate picks among three kernels and their combinations: pair (<= 74), wide (<= 148 /
+    <= 296), wide + pair (297..370), 4-slot rounds, and the same for the remainder after whole rounds of
+    592 (621 = 592 + 29 -> pair, 666 = 592 + 74, 962 = 592 + 370 -> wide + pair).  Every block must come
+    back with its own LUT applied whichever kernel took it."""
+    tables = bench_tables()
+    msgs, cts = _mixed_inputs(keyset, n, 7000 + n)
+    lut_id = ((np.arange(n) * 3 + 1) % 8).astype(np.uint32)
+    out = engine.ks_pbs(cts, lut_id, tables)
+    want = tables[lut_id, msgs]
+    assert np.array_equal(keyset.decrypt(out), want)
+    assert np.abs(keyset.phase_error(out, want)).max() < 2.0**-9
+
+
 def test_blind_rotate_close_to_oracle(engine, keyset):
     """Same small-key LWE in, GPU vs oracle blind rotation: identical up to FFT rounding noise."""
     tables = bench_tables()
