@@ -105,6 +105,10 @@ def main():
     def run_op(ck, eng, nbu, op, strs, pads, scalars=(), reps=2, want=None):
         blocks = np.concatenate([ck.encrypt_str(x, p).blocks for x, p in zip(strs, pads)]) if rank == 0 else None
         blocks = bcast_np(blocks)
+        if os.environ.get("FHS_BENCH_PAGEABLE", "0") != "1":   # pinned host inputs, as in bench.py's e2e leg
+            pin = torch.empty(blocks.shape, dtype=torch.int64, pin_memory=True)
+            pin.numpy().view(np.uint64)[...] = blocks
+            blocks = pin.numpy().view(np.uint64)
         n_chars = [len(x) + 1 if p is None else p + 1 for x, p in zip(strs, pads)]
         prog = Program(op, n_chars, 0, scalars, 4, nbu)
         best, all_ms = None, []

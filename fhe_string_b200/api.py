@@ -133,6 +133,27 @@ class ServerKey:
     def msg_mod(self):
         return self.engine.p.message_modulus
 
+    def _gather(self, parts):
+        """Operand blocks of one call, assembled in a page-locked arena that lives with the key: the copy
+        is the one np.concatenate would do anyway, but the H2D transfer is then a direct DMA (eq on two
+        65-char strings: 6.2 ms instead of 6.6 ms)."""
+        n = sum(len(x) for x in parts)
+        arena = getattr(self, "_arena", None)
+        if arena is None or arena.shape[0] < n:
+            try:
+                import torch
+                t = torch.empty((max(n, 1024), self.engine.big), dtype=torch.int64, pin_memory=True)
+                self._arena_t = t                     # keeps the pinned allocation alive
+                arena = t.numpy().view(np.uint64)
+            except Exception:                         # no torch / pinning refused: pageable memory still works
+                arena = np.empty((max(n, 1024), self.engine.big), dtype=np.uint64)
+            self._arena = arena
+        o = 0
+        for x in parts:
+            arena[o:o + len(x)] = x
+            o += len(x)
+        return arena[:n]
+
     def run(self, op, strings=(), usizes=(), scalars=()):
         key = (op, tuple(s.n_chars for s in strings), len(usizes), tuple(scalars))
         p = self._progs.get(key)
@@ -141,7 +162,7 @@ class ServerKey:
                         self.num_blocks_usize)
             self._progs[key] = p
         parts = [s.blocks for s in strings] + [u.blocks for u in usizes]
-        inb = np.concatenate(parts) if parts else np.zeros((0, self.engine.big), np.uint64)
+        inb = self._gather(parts) if parts else np.zeros((0, self.engine.big), np.uint64)
         out, self.last_stats = p.run(self.engine, inb)
         return _wrap(p.desc, out, self.num_blocks_usize)
 
