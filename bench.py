@@ -133,10 +133,19 @@ def string_op_latency(ck, eng):
     return res
 
 
+def host_threads():
+    """All host cores this process may run on.  torchrun exports OMP_NUM_THREADS=1 for every rank, which
+    would make the CPU arm single-threaded under N > 1; the oracle takes an explicit thread count."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_baseline(ks, tables, threads, target_seconds=12.0):
     """Oracle (port of the reference's CPU path) on a bounded sample of the same workload."""
     from oracle import oracle as O
-    threads = threads or O.lib().orc_max_threads()
+    threads = threads or max(O.lib().orc_max_threads(), host_threads())
     msgs, cts, lut_id = synth_inputs(ks, 2 * threads, seed=4242)
     t0 = time.perf_counter()
     ks.ks_pbs_batch(cts, lut_id, tables, threads=threads)
@@ -163,7 +172,7 @@ def run_reference(args):
     from oracle import oracle as O
     ks = O.Keyset(seed=1)
     tables = bench_tables()
-    threads = O.lib().orc_max_threads()
+    threads = max(O.lib().orc_max_threads(), host_threads())   # not torchrun's OMP_NUM_THREADS=1
     n = 4 * threads                                   # bounded sample of one 4096-block step
     msgs, cts, lut_id = synth_inputs(ks, n, seed=7)
     for _ in range(args.warmup):
