@@ -469,6 +469,21 @@ static void add_external_product(const orc_keyset *ks, uint32_t i, const uint64_
     for (uint32_t c = 0; c < k1; c++) fft_bwd_add_torus(ks, fout + (size_t)c * H, acc + (size_t)c * N);
 }
 
+/* Exposed for tests/test_cpu_oracle_first_principles.py: one acc += GGSW_i (x) ct1 step, so that the
+ * FFT algebra above can be compared with an exact integer negacyclic convolution. */
+void orc_external_product(const orc_keyset *ks, uint32_t i, const uint64_t *ct1, uint64_t *acc) {
+    const uint32_t N = ks->p.poly_size, k1 = ks->p.glwe_dim + 1;
+    uint64_t *states = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)k1 * N);
+    int64_t *dig = (int64_t *)malloc(sizeof(int64_t) * (size_t)k1 * N);
+    cplx *fdig = (cplx *)malloc(sizeof(cplx) * (N / 2));
+    cplx *fout = (cplx *)malloc(sizeof(cplx) * (size_t)k1 * (N / 2));
+    add_external_product(ks, i, ct1, acc, dig, states, fdig, fout);
+    free(states);
+    free(dig);
+    free(fdig);
+    free(fout);
+}
+
 /* A.6 / a1.6 blind rotation */
 void orc_blind_rotate(const orc_keyset *ks, const uint64_t *lwe, uint64_t *acc) {
     const orc_params *p = &ks->p;

@@ -80,6 +80,9 @@ void orc_keyswitch(const orc_keyset *ks, const uint64_t *lwe_big, uint64_t *lwe_
 uint64_t orc_modswitch(const orc_params *p, uint64_t x);
 /* a1.6 blind_rotate_assign on an accumulator (in place). */
 void orc_blind_rotate(const orc_keyset *ks, const uint64_t *lwe_small, uint64_t *acc);
+/* one step of a1.6: acc += GGSW_i (x) ct1 (decompose, forward FFT, Fourier BSK contraction, inverse
+ * FFT, torus add); ct1 and acc are GLWE ciphertexts of (k+1)*N u64.  For first-principles tests. */
+void orc_external_product(const orc_keyset *ks, uint32_t i, const uint64_t *ct1, uint64_t *acc);
 /* a1.7 extract_lwe_sample_from_glwe_ciphertext at coefficient 0. */
 void orc_sample_extract(const orc_params *p, const uint64_t *acc, uint64_t *lwe_big_out);
 /* a1.3 keyswitch_programmable_bootstrap: full KS-PBS of one block. */
