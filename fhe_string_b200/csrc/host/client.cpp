@@ -3,12 +3,18 @@
 // KS-PBS parameter sets, block / string encryption under the big key, decryption.  This is one-off
 // CPU work in the reference as well (tfhe-rs gen_keys_radix, RadixClientKey::encrypt) and is not on
 // the accelerated path; it exists so that the package is usable without any test infrastructure.
-// Randomness: xoshiro256** seeded from the OS (or a caller seed for reproducible benchmarks) --
-// NOT a cryptographic generator (tfhe-rs uses an AES-CTR CSPRNG); documented in DESIGN.md.
+// Randomness: ChaCha20 (RFC 8439 block function, 64-bit block counter + 64-bit stream id) keyed with
+// TWO independent 256-bit keys drawn from the OS (getrandom): one for everything secret (key bits, noise),
+// one for the public masks (KSK / BSK rows, ciphertext a-vectors) -- the split tfhe-rs makes between its
+// secret and encryption generators (concrete-csprng, AES-CTR there).  Public masks are raw generator
+// output, so the generator must be one whose output does not reveal its key; ADVICE r1 showed that the
+// earlier xoshiro256** streams did.  A caller seed != 0 derives both keys from that 64-bit value: the
+// REPRODUCIBLE TEST / BENCH MODE, at most 64 bits of security, never for real data (README).
+#include <sys/random.h>
+
 #include <cmath>
 #include <cstdio>
 #include <cstring>
-#include <random>
 #include <string>
 #include <thread>
 #include <vector>
@@ -17,19 +23,39 @@
 
 namespace {
 
+struct ChaKey { uint32_t w[8]; };
+
+inline uint32_t rotl32(uint32_t x, int k) { return (x << k) | (x >> (32 - k)); }
+#define FHS_QR(a, b, c, d) \
+    a += b; d ^= a; d = rotl32(d, 16); c += d; b ^= c; b = rotl32(b, 12); \
+    a += b; d ^= a; d = rotl32(d, 8);  c += d; b ^= c; b = rotl32(b, 7);
+
+// One ChaCha20 keystream per (key, stream id); 64-byte blocks, 64-bit block counter.
 struct Rng {
-    uint64_t s[4];
-    explicit Rng(uint64_t seed, uint64_t stream) {
-        uint64_t x = seed * 0x9E3779B97F4A7C15ull + stream * 0xD1B54A32D192ED03ull + 0x8CB92BA72F3D8DD7ull;
-        for (auto &v : s) { x += 0x9E3779B97F4A7C15ull; uint64_t z = x; z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-                            z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; v = z ^ (z >> 31); }
+    uint32_t st[16];
+    uint64_t buf[8];
+    int pos = 8;
+    Rng(const ChaKey &key, uint64_t stream) {
+        st[0] = 0x61707865u; st[1] = 0x3320646eu; st[2] = 0x79622d32u; st[3] = 0x6b206574u;
+        for (int i = 0; i < 8; i++) st[4 + i] = key.w[i];
+        st[12] = 0; st[13] = 0;
+        st[14] = (uint32_t)stream; st[15] = (uint32_t)(stream >> 32);
     }
-    static uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
-    uint64_t next() {
-        const uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17;
-        s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45);
-        return r;
+    void refill() {
+        uint32_t x[16];
+        for (int i = 0; i < 16; i++) x[i] = st[i];
+        for (int r = 0; r < 10; r++) {
+            FHS_QR(x[0], x[4], x[8], x[12]) FHS_QR(x[1], x[5], x[9], x[13])
+            FHS_QR(x[2], x[6], x[10], x[14]) FHS_QR(x[3], x[7], x[11], x[15])
+            FHS_QR(x[0], x[5], x[10], x[15]) FHS_QR(x[1], x[6], x[11], x[12])
+            FHS_QR(x[2], x[7], x[8], x[13]) FHS_QR(x[3], x[4], x[9], x[14])
+        }
+        for (int i = 0; i < 8; i++)
+            buf[i] = (uint64_t)(x[2 * i] + st[2 * i]) | ((uint64_t)(x[2 * i + 1] + st[2 * i + 1]) << 32);
+        if (++st[12] == 0) ++st[13];
+        pos = 0;
     }
+    uint64_t next() { if (pos == 8) refill(); return buf[pos++]; }
     double unit() { return ((double)(next() >> 11) + 0.5) * (1.0 / 9007199254740992.0); }
     uint64_t torus_noise(double std) {  // round(N(0, (std 2^64)^2)) mod 2^64
         const double u1 = unit(), u2 = unit();
@@ -37,6 +63,17 @@ struct Rng {
         return (uint64_t)(int64_t)std::llrint(g * std * 18446744073709551616.0);
     }
 };
+#undef FHS_QR
+
+bool os_random(void *dst, size_t n) {
+    uint8_t *p = (uint8_t *)dst;
+    while (n) {
+        ssize_t got = getrandom(p, n, 0);
+        if (got <= 0) return false;
+        p += got; n -= (size_t)got;
+    }
+    return true;
+}
 
 }  // namespace
 
@@ -45,7 +82,9 @@ struct fhs_client_key {
     double lwe_std, glwe_std;
     uint32_t nb_char, nb_usize;
     size_t max_len;
-    uint64_t seed, enc_counter = 0;
+    ChaKey secret_key, public_key;         // secret: key bits + noise; public: masks
+    uint64_t enc_counter = 0;
+    bool reproducible = false;             // keys derived from a caller seed (test / bench mode)
     std::vector<uint8_t> lwe_sk, glwe_sk;  // bits
     std::vector<uint64_t> ksk, bsk;        // server key material (fhs_upload_keys layouts)
 };
@@ -66,12 +105,12 @@ void gen_ksk(fhs_client_key &k, int nthreads) {
     k.ksk.assign((size_t)big * lv * (n + 1), 0);
     auto work = [&](uint32_t i0, uint32_t i1) {
         for (uint32_t i = i0; i < i1; i++) {
-            Rng r(k.seed, 0x10000000ull + i);
+            Rng r(k.public_key, 0x10000000ull + i), e(k.secret_key, 0x10000000ull + i);
             for (uint32_t l = 1; l <= lv; l++) {  // rows level 1 (most significant) .. lv: FHS_KSK_LEVEL_MSB_FIRST
                 uint64_t *row = &k.ksk[((size_t)i * lv + (l - 1)) * (n + 1)];
                 uint64_t dot = 0;
                 for (uint32_t j = 0; j < n; j++) { row[j] = r.next(); if (k.lwe_sk[j]) dot += row[j]; }
-                row[n] = dot + ((uint64_t)k.glwe_sk[i] << (64 - bl * l)) + r.torus_noise(k.lwe_std);
+                row[n] = dot + ((uint64_t)k.glwe_sk[i] << (64 - bl * l)) + e.torus_noise(k.lwe_std);
             }
         }
     };
@@ -90,7 +129,7 @@ void gen_bsk(fhs_client_key &k, int nthreads) {
         for (uint32_t j = 0; j < N; j++) if (k.glwe_sk[c * N + j]) ones[c].push_back(j);
     auto work = [&](uint32_t i0, uint32_t i1) {
         for (uint32_t i = i0; i < i1; i++) {
-            Rng r(k.seed, 0x20000000ull + i);
+            Rng r(k.public_key, 0x20000000ull + i), e(k.secret_key, 0x20000000ull + i);
             const uint64_t bit = k.lwe_sk[i];
             for (uint32_t l = 1; l <= lv; l++) {
                 const uint64_t scale = bit << (64 - bl * l);
@@ -107,7 +146,7 @@ void gen_bsk(fhs_client_key &k, int nthreads) {
                             for (uint32_t t = N - pos; t < N; t++) body[t + pos - N] -= mask[t];
                         }
                     }
-                    for (uint32_t j = 0; j < N; j++) body[j] += r.torus_noise(k.glwe_std);
+                    for (uint32_t j = 0; j < N; j++) body[j] += e.torus_noise(k.glwe_std);
                 }
             }
         }
@@ -123,6 +162,16 @@ extern "C" {
 
 const char *fhs_client_last_error(void) { return c_err.c_str(); }
 
+// Self-test hook: one ChaCha20 block for key[8] and state words 12..15 (RFC 8439 2.3.2 known answer).
+void fhs_chacha20_block(const uint32_t key[8], const uint32_t ctr_nonce[4], uint8_t out[64]) {
+    ChaKey k;
+    memcpy(k.w, key, sizeof(k.w));
+    Rng r(k, 0);
+    for (int i = 0; i < 4; i++) r.st[12 + i] = ctr_nonce[i];
+    r.refill();
+    memcpy(out, r.buf, 64);
+}
+
 int fhs_generate_keys(const fhs_params *params, const double *stds, size_t l, uint64_t seed,
                       fhs_client_key **out) {
     if (!out) return FHS_ERR_INVALID;
@@ -136,10 +185,20 @@ int fhs_generate_keys(const fhs_params *params, const double *stds, size_t l, ui
     k->nb_char = ceil_log(k->p.message_modulus, 128);
     k->nb_usize = std::max<uint32_t>(1, ceil_log(k->p.message_modulus, (uint64_t)l + 1));
     k->max_len = l;
-    if (seed == 0) { std::random_device rd; seed = ((uint64_t)rd() << 32) ^ rd() ^ 0x5DEECE66Dull; }
-    k->seed = seed;
+    if (seed == 0) {
+        if (!os_random(&k->secret_key, sizeof(ChaKey)) || !os_random(&k->public_key, sizeof(ChaKey))) {
+            delete k; c_err = "getrandom failed"; return FHS_ERR_INVALID;
+        }
+    } else {   // reproducible test / bench mode: both keys are functions of the 64-bit seed -- NOT secure
+        ChaKey boot{};
+        boot.w[0] = (uint32_t)seed; boot.w[1] = (uint32_t)(seed >> 32); boot.w[2] = 0x46485321u;
+        Rng d(boot, 0);
+        for (auto &w : k->secret_key.w) w = (uint32_t)d.next();
+        for (auto &w : k->public_key.w) w = (uint32_t)d.next();
+        k->reproducible = true;
+    }
     const uint32_t big = k->p.glwe_dim * k->p.poly_size;
-    Rng r1(seed, 1), r2(seed, 2);
+    Rng r1(k->secret_key, 1), r2(k->secret_key, 2);
     k->glwe_sk.resize(big); for (auto &b : k->glwe_sk) b = (uint8_t)(r1.next() >> 63);
     k->lwe_sk.resize(k->p.lwe_dim); for (auto &b : k->lwe_sk) b = (uint8_t)(r2.next() >> 63);
     int nt = (int)std::thread::hardware_concurrency();
@@ -171,10 +230,11 @@ int fhs_encrypt_blocks(fhs_client_key *k, const uint64_t *msgs, size_t n, uint64
     const uint32_t big = k->p.glwe_dim * k->p.poly_size;
     const uint64_t delta = (1ull << 63) / ((uint64_t)k->p.message_modulus * k->p.carry_modulus);
     for (size_t b = 0; b < n; b++) {
-        Rng r(k->seed, 0x30000000ull + k->enc_counter++);
+        const uint64_t id = 0x30000000ull + k->enc_counter++;
+        Rng r(k->public_key, id), e(k->secret_key, id);
         uint64_t *ct = out + b * (big + 1), dot = 0;
         for (uint32_t j = 0; j < big; j++) { ct[j] = r.next(); if (k->glwe_sk[j]) dot += ct[j]; }
-        ct[big] = dot + msgs[b] * delta + r.torus_noise(k->glwe_std);
+        ct[big] = dot + msgs[b] * delta + e.torus_noise(k->glwe_std);
     }
     return FHS_OK;
 }

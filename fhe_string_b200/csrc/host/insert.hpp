@@ -19,9 +19,9 @@ struct InsertOps : ReplaceOps {
 
     Buf buf_of(const FStr &s) {
         Buf b;
-        b.max_len = s.ch.size() - 1;
+        b.true_max = s.ch.size() - 1;
         for (size_t i = 0; i + 1 < s.ch.size(); i++) b.ch.push_back(s.ch[i]);
-        b.len = len(s);
+        b.len = fit(len(s), digits_for(b.true_max));
         return b;
     }
     FStr str_of(const Buf &b, size_t l) {
@@ -30,30 +30,6 @@ struct InsertOps : ReplaceOps {
         for (size_t j = 0; j < l; j++) out.ch.push_back(j < b.ch.size() ? b.ch[j] : z);
         out.ch.push_back(z);  // terminator
         return out;
-    }
-
-    // min(x + y, cap) without wrapping mod 4^nb_usize: one extra (most significant) block
-    Rad add_len_clamped(const Rad &x, const Rad &y, size_t cap) {
-        Rad xe = x, ye = y;
-        xe.push_back(Graph::constant(0));
-        ye.push_back(Graph::constant(0));
-        Rad s = add_rad(xe, ye);
-        Bool over = gt_scalar(s, cap);
-        Rad r = if_then_else(over, scalar(cap, s.size()), s);
-        r.pop_back();    // <= cap < 4^nb_usize
-        for (auto &blk : r) blk = g.pbs(blk, [](int v) { return v & 3; }, 0, 3);   // fresh digits for the shifter
-        return r;
-    }
-    // replace.hpp concat with the tracked length clamped to the capacity, so that a full buffer
-    // shifts everything appended later out of range instead of wrapping around
-    Buf concat_c(const Buf &A, const Buf &B, size_t limit) {
-        Buf R;
-        R.max_len = std::min(A.max_len + B.max_len, limit);
-        const size_t cap = R.max_len;
-        std::vector<Rad> bs = shift_right(B.ch, A.len, A.max_len, cap);
-        for (size_t j = 0; j < cap; j++) R.ch.push_back(j < A.ch.size() ? add_chars(A.ch[j], bs[j]) : bs[j]);
-        R.len = add_len_clamped(A.len, B.len, cap);
-        return R;
     }
 
     // insert.rs:14
@@ -67,25 +43,23 @@ struct InsertOps : ReplaceOps {
         const size_t l = std::min(a.ch.size() - 1 + b.ch.size() - 1, max_str_len());
         Buf head;
         FStr h = substr_to(a, index);
-        head.max_len = a.ch.size() - 1;
+        head.true_max = a.ch.size() - 1;
         for (size_t i = 0; i + 1 < h.ch.size(); i++) head.ch.push_back(h.ch[i]);
         head.len = index;
         FStr t = shift_left(a, index);
         Buf tail = buf_of(a);            // same capacity; its length is not needed afterwards
         for (size_t i = 0; i + 1 < t.ch.size(); i++) tail.ch[i] = t.ch[i];
-        Buf hb = concat_c(head, buf_of(b), l);
+        Buf hb = concat(head, buf_of(b), l);
         return str_of(concat(hb, tail, l), l);
     }
 
     // insert.rs:20; clear capacity l as in the reference (clamped to the maximum string length)
     FStr repeat(const FStr &a, const Rad &n, size_t l) {
         l = std::min(l, max_str_len());
-        Buf pw = buf_of(a);              // a^(2^k), truncated to l chars, length clamped to its capacity
-        if (pw.max_len > l) {
-            pw.ch.resize(l);
-            pw.max_len = l;
-            pw.len = add_len_clamped(pw.len, usize(0), l);
-        }
+        // a^(2^k): the buffer is truncated to l chars, the tracked length is not (replace.hpp Buf), so a
+        // full buffer shifts everything appended later out of range
+        Buf pw = buf_of(a);
+        if (pw.ch.size() > l) pw.ch.resize(l);
         Buf acc;
         bool have = false;
         const size_t nbits = 2 * n.size();
@@ -93,15 +67,15 @@ struct InsertOps : ReplaceOps {
             Bool bit = (k & 1) ? bit1(n[k / 2]) : bit0(n[k / 2]);
             if (!(bit.is_const() && bit.c == 0)) {
                 Buf term;
-                term.max_len = pw.max_len;
+                term.true_max = pw.true_max;
                 for (auto &c : pw.ch) term.ch.push_back(select_zero(bit, c));
                 term.len = select_zero(bit, pw.len);
-                acc = have ? concat_c(acc, term, l) : term;
+                acc = have ? concat(acc, term, l) : term;
                 have = true;
             }
-            if (k + 1 < nbits) pw = concat_c(pw, pw, l);
+            if (k + 1 < nbits) pw = concat(pw, pw, l);
         }
-        if (!have) { acc.max_len = 0; acc.len = usize(0); }
+        if (!have) { acc.true_max = 0; acc.len = Rad{Graph::constant(0)}; }
         return str_of(acc, l);
     }
 

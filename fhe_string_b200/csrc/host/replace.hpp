@@ -12,8 +12,19 @@ namespace fhs_host {
 struct ReplaceOps : SplitOps {
     using SplitOps::SplitOps;
 
-    struct Buf { std::vector<Rad> ch; Rad len; size_t max_len; };  // chars beyond len are 0
+    // chars beyond len are 0.  `ch` holds min(true_max, l) chars (the output capacity l truncates the
+    // BUFFER, replace.rs:45-101 keeps the first l chars of the result); `len` is the untruncated length
+    // in as many base-4 digits as `true_max` needs, so it neither wraps at FheUsize::max nor lags behind
+    // the buffer when the result is longer than l.
+    struct Buf { std::vector<Rad> ch; Rad len; size_t true_max; };
 
+    static size_t digits_for(size_t v) { size_t w = 1; while (w < 32 && (v >> (2 * w)) != 0) w++; return w; }
+    // same value in `w` digits: constant zeros appended, provably-zero top digits dropped
+    static Rad fit(Rad r, size_t w) {
+        while (r.size() < w) r.push_back(Graph::constant(0));
+        r.resize(w);
+        return r;
+    }
     static bool rad_is_zero_const(const Rad &r) {
         for (auto &b : r) if (!(b.is_const() && b.c == 0)) return false;
         return true;
@@ -23,17 +34,20 @@ struct ReplaceOps : SplitOps {
         for (size_t k = 0; k < x.size(); k++) r.push_back(bounded(add(x[k], y[k]), 0, 3));
         return r;
     }
-    // B shifted right by `amount` (<= max_amount) inside a buffer of `cap` chars
+    // B shifted right by `amount` (<= max_amount) inside a buffer of `cap` chars; a shift of cap or more
+    // leaves nothing of B in the buffer
     std::vector<Rad> shift_right(const std::vector<Rad> &b, const Rad &amount, size_t max_amount, size_t cap) {
         Rad z = zero_char();
         std::vector<Rad> cur(cap, z);
         for (size_t j = 0; j < std::min(cap, b.size()); j++) cur[j] = b[j];
+        std::vector<Bool> overflow;
         for (size_t blk = 0; blk < amount.size(); blk++) {
             for (int bit = 0; bit < 2; bit++) {
                 const size_t sh = (size_t)1 << (2 * blk + bit);
-                if (sh > max_amount) return cur;
+                if (sh > max_amount) break;
                 Bool sb = bit ? bit1(amount[blk]) : bit0(amount[blk]);
                 if (sb.is_const() && sb.c == 0) continue;
+                if (sh >= cap) { overflow.push_back(sb); continue; }
                 std::vector<Rad> nx(cap);
                 for (size_t j = 0; j < cap; j++) {
                     const Rad &from = (j >= sh) ? cur[j - sh] : z;
@@ -43,16 +57,21 @@ struct ReplaceOps : SplitOps {
                 cur.swap(nx);
             }
         }
+        if (!overflow.empty()) {
+            Bool keep = bnot(any(overflow));
+            for (size_t j = 0; j < cap; j++)
+                if (!rad_is_zero_const(cur[j])) cur[j] = select_zero(keep, cur[j]);
+        }
         return cur;
     }
     Buf concat(const Buf &A, const Buf &B, size_t limit) {
         Buf R;
-        R.max_len = std::min(A.max_len + B.max_len, limit);
-        const size_t cap = R.max_len;
-        std::vector<Rad> bs = shift_right(B.ch, A.len, A.max_len, cap);
-        Rad z = zero_char();
+        R.true_max = A.true_max + B.true_max;
+        const size_t cap = std::min(R.true_max, limit);
+        std::vector<Rad> bs = shift_right(B.ch, A.len, A.true_max, cap);
         for (size_t j = 0; j < cap; j++) R.ch.push_back(j < A.ch.size() ? add_chars(A.ch[j], bs[j]) : bs[j]);
-        R.len = add_rad(A.len, B.len);
+        const size_t w = digits_for(R.true_max);
+        R.len = add_rad(fit(A.len, w), fit(B.len, w));
         return R;
     }
 
@@ -83,17 +102,17 @@ struct ReplaceOps : SplitOps {
             cov = bounded(cov, 0, 1);
             if (Ms > 0) {
                 Buf seg;
-                seg.max_len = Ms;
+                seg.true_max = Ms;
                 for (size_t t = 0; t < Ms; t++) seg.ch.push_back(select_zero(chosen[i], s.ch[t]));
-                seg.len = select_zero(chosen[i], slen);
+                seg.len = fit(select_zero(chosen[i], slen), digits_for(Ms));
                 nodes.push_back(seg);
             }
             Buf lit;
-            lit.max_len = 1;
+            lit.true_max = 1;
             Bool keep = bnot(cov);
             lit.ch.push_back(select_zero(keep, a.ch[i]));
             Bool nonzero = g.pbs(add(keep, bnot(az[i])), [](int x) { return x == 2; }, 0, 1);
-            lit.len = from_bool(nonzero, nb_usize);
+            lit.len = from_bool(nonzero, 1);
             nodes.push_back(lit);
         }
         while (nodes.size() > 1) {

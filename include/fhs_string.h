@@ -93,6 +93,11 @@ int fhs_generate_keys(const fhs_params *params /* NULL: PARAM_MESSAGE_2_CARRY_2_
                       fhs_client_key **out);
 void fhs_client_key_destroy(fhs_client_key *k);
 const char *fhs_client_last_error(void);
+/* Self-test hook for the client's generator (ChaCha20 block function, RFC 8439 2.3.2): state words
+ * 12..15 = ctr_nonce.  Keys, masks and noise come from this generator keyed from the OS (getrandom,
+ * 2 x 256 bit: one key for secrets and noise, one for public masks) when seed == 0; a non-zero seed is
+ * the reproducible test / bench mode and is NOT secure (64-bit seed). */
+void fhs_chacha20_block(const uint32_t key[8], const uint32_t ctr_nonce[4], uint8_t out[64]);
 int fhs_client_key_info(const fhs_client_key *k, fhs_params *p, uint32_t *num_blocks_char,
                         uint32_t *num_blocks_usize, size_t *max_len);
 /* Server key material in the layouts fhs_upload_keys takes (KSK level order MSB first). */
