@@ -185,7 +185,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
                        const uint64_t *__restrict__ lut_tables, const double2 *__restrict__ bsk_f,
                        const double2 *__restrict__ twiddle_g, uint64_t *__restrict__ lwe_out,
                        unsigned int batch, int n_lwe, int log_box, uint64_t delta, int active_slots,
-                       int stagger_rt) {
+                       int stagger_rt, unsigned int n_luts) {
     // active_slots in {1, 2, 4}: small levels use fewer ciphertexts per CTA (more CTAs, shorter
     // iterations); idle compute / loader warps skip the main loops entirely.
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -296,7 +296,7 @@ blind_rotate_v2_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *_
             {
                 // a1.1 + rotation by X^{-b~}: this thread's 64 coefficients -> TMEM + hi plane
                 const uint32_t bt = modswitch(lwe[n_lwe]);
-                const uint64_t *__restrict__ tab = lut_tables + (size_t)lut_id[ct] * table_len;
+                const uint64_t *__restrict__ tab = lut_tables + (size_t)min(lut_id[ct], n_luts - 1u) * table_len;
                 uint32_t vhi[64];
 #pragma unroll
                 for (int q = 0; q < 64; q++) {
@@ -664,48 +664,43 @@ int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc) {
     return FHS_OK;
 }
 
+// Dispatch of one level of `batch` blind rotations over the three kernels (all limits per context):
+//   <= pair_limit (one ciphertext per two SMs, every cluster resident)  -> pair kernel, 1 wave
+//   <= wide_limit (2 per SM)                                            -> wide kernel, 1 wave
+//   otherwise whole 4-slot rounds of the throughput kernel, and the remainder as one pair wave, one wide
+//   wave, or wide + pair when that is cheaper than one more 4-slot round.
 int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
-                        const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
+                        const uint64_t *d_tables, size_t n_luts, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
-    {   // small levels: 4 warps per ciphertext (FHS_BR_WIDE=0 disables, =N sets the batch limit)
-        static long wide_limit = -1;
-        if (wide_limit < 0) {
-            const char *e = getenv("FHS_BR_WIDE");
-            wide_limit = e ? atol(e) : 2L * c->sm_count;
+    if (n_luts == 0) { set_error("blind rotation without a LUT"); return FHS_ERR_INVALID; }
+    const long wide_limit = c->knobs.wide_limit;
+    const long pair_cap = c->knobs.pair_on ? blind_rotate_pair_limit(c) : 0;
+    const size_t in_w = (size_t)c->n + 1, out_w = (size_t)c->big + 1;
+    auto small_wave = [&](size_t lo, size_t nb) -> int {   // nb <= max(pair_cap, wide_limit)
+        if ((long)nb <= pair_cap)
+            return launch_blind_rotate_pair(c, d_small + lo * in_w, d_lut_id + lo, d_tables, n_luts, nb, d_out + lo * out_w);
+        return launch_blind_rotate_wide(c, d_small + lo * in_w, d_lut_id + lo, d_tables, n_luts, nb, d_out + lo * out_w);
+    };
+    if ((long)batch <= pair_cap || (long)batch <= wide_limit) return small_wave(0, batch);
+    {
+        const size_t round4 = (size_t)kSlots2 * c->sm_count, rem = batch % round4, head = batch - rem;
+        // a remainder of at most 2 ciphertexts per SM after whole 4-slot rounds is cheaper as a separate
+        // small wave (1.7 / 2.3 / 3.6 ms) than as one more 4-slot round (6.2 ms)
+        if (rem > 0 && ((long)rem <= wide_limit || (long)rem <= pair_cap)) {
+            int rc = launch_blind_rotate(c, d_small, d_lut_id, d_tables, n_luts, head, d_out);
+            if (rc != FHS_OK) return rc;
+            return small_wave(head, rem);
         }
-        if ((long)batch <= wide_limit) return launch_blind_rotate_wide(c, d_small, d_lut_id, d_tables, batch, d_out);
-        // a remainder of at most 2 ciphertexts per SM after whole 4-slot rounds is cheaper as a
-        // separate wide launch (2.3 / 3.8 ms) than as one more 4-slot round (6.2 ms)
-        const size_t round4 = (size_t)kSlots2 * c->sm_count, rem = batch % round4;
-        if (rem > 0 && (long)rem <= wide_limit) {
-            const size_t head = batch - rem;
-            int rc = launch_blind_rotate(c, d_small, d_lut_id, d_tables, head, d_out);
+        // up to one pair wave above two ciphertexts per SM: wide (3.6 ms) + pair (1.7 ms) instead of one
+        // more 4-slot round (5.9 ms)
+        if (wide_limit > 0 && pair_cap > 0 && (long)rem > wide_limit && (long)rem <= wide_limit + pair_cap) {
+            int rc = head ? launch_blind_rotate(c, d_small, d_lut_id, d_tables, n_luts, head, d_out) : FHS_OK;
             if (rc != FHS_OK) return rc;
-            return launch_blind_rotate_wide(c, d_small + head * ((size_t)c->n + 1), d_lut_id + head, d_tables, rem,
-                                            d_out + head * ((size_t)c->big + 1));
-        }
-        // a remainder of up to one pair wave above two ciphertexts per SM: wide (3.6 ms) + pair (1.7 ms)
-        // instead of one more 4-slot round (5.9 ms)
-        const long pair_cap = blind_rotate_pair_limit(c);
-        if (wide_limit == 2L * c->sm_count && pair_cap > 0 && (long)rem > wide_limit && (long)rem <= wide_limit + pair_cap) {
-            const size_t head = batch - rem, mid = (size_t)wide_limit;
-            int rc = head ? launch_blind_rotate(c, d_small, d_lut_id, d_tables, head, d_out) : FHS_OK;
-            if (rc != FHS_OK) return rc;
-            rc = launch_blind_rotate_wide(c, d_small + head * ((size_t)c->n + 1), d_lut_id + head, d_tables, mid,
-                                          d_out + head * ((size_t)c->big + 1));
-            if (rc != FHS_OK) return rc;
-            const size_t h2 = head + mid;
-            return launch_blind_rotate_wide(c, d_small + h2 * ((size_t)c->n + 1), d_lut_id + h2, d_tables, rem - mid,
-                                            d_out + h2 * ((size_t)c->big + 1));
+            if ((rc = small_wave(head, (size_t)wide_limit)) != FHS_OK) return rc;
+            return small_wave(head + (size_t)wide_limit, rem - (size_t)wide_limit);
         }
     }
-    static bool knobs_read = false;
-    static int stagger = 4, opt = 13;  // dev knobs: FHS_BR_STAGGER (0 | 3 | 4), FHS_BR_OPT (0 | 1 | 5 | 13)
-    if (!knobs_read) {
-        knobs_read = true;
-        if (const char *e = getenv("FHS_BR_STAGGER")) stagger = atoi(e);
-        if (const char *e = getenv("FHS_BR_OPT")) opt = atoi(e) & 13;
-    }
+    const int stagger = c->knobs.stagger, opt = c->knobs.opt;
     if (!c->attr_br) {
 #define FHS_BR_ATTR(o, st) FHS_CUDA(cudaFuncSetAttribute(blind_rotate_v2_kernel<o, st>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem2Bytes))
         FHS_BR_ATTR(0, 0); FHS_BR_ATTR(1, 3); FHS_BR_ATTR(5, 3); FHS_BR_ATTR(13, 3);
@@ -723,7 +718,7 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
         // token barriers next to the transposes, which it does not for the compile-time variants.
         const int st = stagger;
         using kern_t = void (*)(const uint64_t *, const uint32_t *, const uint64_t *, const double2 *,
-                                const double2 *, uint64_t *, unsigned int, int, int, uint64_t, int, int);
+                                const double2 *, uint64_t *, unsigned int, int, int, uint64_t, int, int, unsigned int);
         // FHS_BR_OPT=0 FHS_BR_STAGGER=0 selects the round-1 baseline kernel (A/B runs); default is
         // the TMEM-twiddle kernel with the stagger flag on (4); 3 = same kernel, flag off.
         kern_t kern = (opt == 0 && st == 0) ? blind_rotate_v2_kernel<0, 0>
@@ -732,7 +727,7 @@ int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_i
         const int stagger_rt = st == 4;
         kern<<<(unsigned)ctas, kThreads2, kSmem2Bytes, c->stream>>>(
             d_small, d_lut_id, d_tables, c->d_bsk_f, c->d_twiddle, d_out, (unsigned int)batch,
-            (int)c->n, log_box, delta, active, stagger_rt);
+            (int)c->n, log_box, delta, active, stagger_rt, (unsigned int)n_luts);
     }
     c->launches++;
     FHS_CUDA(cudaGetLastError());

@@ -140,7 +140,8 @@ __device__ __forceinline__ void p_store_tw(uint32_t (&tw)[32], int n, double c, 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPThreads, 1)
 blind_rotate_pair_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__restrict__ lut_id,
                          const uint64_t *__restrict__ lut_tables, const double2 *__restrict__ bsk_x,
-                         uint64_t *__restrict__ lwe_out, int n_lwe, int log_box, uint64_t delta) {
+                         uint64_t *__restrict__ lwe_out, int n_lwe, int log_box, uint64_t delta,
+                         unsigned int n_luts) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     // the pad is the same in both CTAs of the pair (same kernel, same dynamic shared memory window), so a
     // local shared address maps to the peer's copy of the same field
@@ -235,7 +236,7 @@ blind_rotate_pair_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
         for (int x = t; x < n_lwe; x += 128) sm.amod[x] = (uint16_t)p_modswitch(lwe[x]);
         {   // a1.1 + rotation by X^{-b~}: this thread's 16 coefficients -> TMEM + hi plane
             const uint32_t bt = p_modswitch(lwe[n_lwe]);
-            const uint64_t *__restrict__ tab = lut_tables + (size_t)lut_id[cti] * table_len;
+            const uint64_t *__restrict__ tab = lut_tables + (size_t)min(lut_id[cti], n_luts - 1u) * table_len;
             uint32_t vhi[16];
 #pragma unroll
             for (int x = 0; x < 16; x++) {
@@ -513,12 +514,12 @@ int blind_rotate_pair_limit(Ctx *c) {
 }
 
 int launch_blind_rotate_pair(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
-                             const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
+                             const uint64_t *d_tables, size_t n_luts, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
     const int log_box = p_ilog2(kN / c->space);
     const uint64_t delta = (1ull << 63) / c->space;
     blind_rotate_pair_kernel<<<(unsigned)(2 * batch), kPThreads, kPSmemBytes, c->stream>>>(
-        d_small, d_lut_id, d_tables, c->d_bsk_x, d_out, (int)c->n, log_box, delta);
+        d_small, d_lut_id, d_tables, c->d_bsk_x, d_out, (int)c->n, log_box, delta, (unsigned int)n_luts);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     return FHS_OK;

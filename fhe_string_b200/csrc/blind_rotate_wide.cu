@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kWThreads, 1)
 blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t *__restrict__ lut_id,
                          const uint64_t *__restrict__ lut_tables, const double2 *__restrict__ bsk_w,
                          uint64_t *__restrict__ lwe_out, unsigned int batch, int n_lwe, int log_box,
-                         uint64_t delta, int active_cts) {
+                         uint64_t delta, int active_cts, unsigned int n_luts) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t smem_pad = (0u - (uint32_t)__cvta_generic_to_shared(smem_raw)) & 8191u;
     WSmem &sm = *reinterpret_cast<WSmem *>(smem_raw + smem_pad);
@@ -214,7 +214,7 @@ blind_rotate_wide_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
             for (int x = threadIdx.x & 127; x < n_lwe; x += 128) sm.amod[ct][x] = (uint16_t)w_modswitch(lwe[x]);
             {   // a1.1 + rotation by X^{-b~}: this thread's 32 coefficients -> TMEM + hi plane
                 const uint32_t bt = w_modswitch(lwe[n_lwe]);
-                const uint64_t *__restrict__ tab = lut_tables + (size_t)lut_id[cti] * table_len;
+                const uint64_t *__restrict__ tab = lut_tables + (size_t)min(lut_id[cti], n_luts - 1u) * table_len;
                 uint32_t vhi[32];
 #pragma unroll
                 for (int x = 0; x < 32; x++) {
@@ -438,18 +438,10 @@ int w_ilog2(uint32_t x) {
 
 }  // namespace
 
+// One wave of the wide kernel (the caller, launch_blind_rotate, picks the kernel per wave).
 int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
-                             const uint64_t *d_tables, size_t batch, uint64_t *d_out) {
+                             const uint64_t *d_tables, size_t n_luts, size_t batch, uint64_t *d_out) {
     if (batch == 0) return FHS_OK;
-    {   // smallest levels: one ciphertext per pair of SMs (FHS_BR_PAIR=0 disables)
-        static int pair_on = -1;
-        if (pair_on < 0) {
-            const char *e = getenv("FHS_BR_PAIR");
-            pair_on = e ? atoi(e) : 1;
-        }
-        if (pair_on && (long)batch <= (long)blind_rotate_pair_limit(c))
-            return launch_blind_rotate_pair(c, d_small, d_lut_id, d_tables, batch, d_out);
-    }
     if (!c->attr_brw) {
         FHS_CUDA(cudaFuncSetAttribute(blind_rotate_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)kWSmemBytes));
@@ -461,7 +453,7 @@ int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_
     size_t ctas = (batch + active - 1) / active;
     if (ctas > (size_t)c->sm_count) ctas = c->sm_count;
     blind_rotate_wide_kernel<<<(unsigned)ctas, kWThreads, kWSmemBytes, c->stream>>>(
-        d_small, d_lut_id, d_tables, c->d_bsk_w, d_out, (unsigned int)batch, (int)c->n, log_box, delta, active);
+        d_small, d_lut_id, d_tables, c->d_bsk_w, d_out, (unsigned int)batch, (int)c->n, log_box, delta, active, (unsigned int)n_luts);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     return FHS_OK;

@@ -91,6 +91,21 @@ void fhs_default_params(fhs_params *p) {
 const char *fhs_last_error(void) { return fhs::g_err; }
 int fhs_version(void) { return 100; }
 
+static int ctx_init(Ctx *c, int device);
+
+static void read_knobs(Ctx *c) {
+    auto env_int = [](const char *name, long dflt) { const char *e = getenv(name); return e ? atol(e) : dflt; };
+    c->knobs.wide_limit = env_int("FHS_BR_WIDE", 2L * c->sm_count);
+    c->knobs.pair_on = (int)env_int("FHS_BR_PAIR", 1);
+    c->knobs.stagger = (int)env_int("FHS_BR_STAGGER", 4);
+    c->knobs.opt = (int)env_int("FHS_BR_OPT", 13) & 13;
+    c->knobs.ks_variant = (int)env_int("FHS_KS_VARIANT", 3);
+    c->knobs.ks_umma_min = (int)env_int("FHS_KS_UMMA_MIN", 1);
+    c->knobs.ks_mma_min = (int)env_int("FHS_KS_MMA_MIN", 1);
+    c->knobs.bsk_f64 = env_int("FHS_BSK_XF", 1) == 0;
+    c->knobs.ks_baseline_keys = c->knobs.ks_variant != 3 || c->knobs.ks_umma_min > 1;
+}
+
 int fhs_ctx_create(int device, fhs_ctx **out) {
     if (!out) return FHS_ERR_INVALID;
     *out = nullptr;
@@ -109,15 +124,25 @@ int fhs_ctx_create(int device, fhs_ctx **out) {
     Ctx *c = new (std::nothrow) Ctx();
     if (!c) return FHS_ERR_OOM;
     c->device = device;
+    const int rc = ctx_init(c, device);
+    if (rc != FHS_OK) {          // release whatever was created before the failing call
+        fhs_ctx_destroy(reinterpret_cast<fhs_ctx *>(c));
+        return rc;
+    }
+    *out = reinterpret_cast<fhs_ctx *>(c);
+    return FHS_OK;
+}
+
+static int ctx_init(Ctx *c, int device) {
     cudaDeviceProp prop;
     FHS_CUDA(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
     if (prop.major < 10) {
         fhs::set_error("device %d is sm_%d%d; this library is built for sm_100a only", device,
                        prop.major, prop.minor);
-        delete c;
         return FHS_ERR_CUDA;
     }
+    read_knobs(c);
     FHS_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
     {   // ciphertext pools use the stream-ordered allocator (level.cu): keep freed blocks cached
@@ -140,7 +165,6 @@ int fhs_ctx_create(int device, fhs_ctx **out) {
         }
     FHS_CUDA(cudaMalloc(&c->d_twiddle, T.size() * sizeof(double2)));
     FHS_CUDA(cudaMemcpy(c->d_twiddle, T.data(), T.size() * sizeof(double2), cudaMemcpyHostToDevice));
-    *out = reinterpret_cast<fhs_ctx *>(c);
     return FHS_OK;
 }
 
@@ -148,7 +172,7 @@ void fhs_ctx_destroy(fhs_ctx *h) {
     if (!h) return;
     Ctx *c = reinterpret_cast<Ctx *>(h);
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    if (c->stream) cudaStreamSynchronize(c->stream);
     fhs::comm_release(c);
     fhs::free_keys(c);
     cudaFree(c->d_twiddle);
@@ -243,9 +267,13 @@ static int upload_keys_impl(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk
     int rc = FHS_OK;
     do {
         cudaError_t e;
+        // the tcgen05 keyswitch needs only its own operand tiles; the digit-order key is a staging
+        // buffer for the tilers, and the key forms of the two baseline kernels (offset-correction row,
+        // mma.sync tiles; ~120 MB and ~1.3 ms of upload kernels) exist only for A/B contexts
+        const bool base = c->knobs.ks_baseline_keys;
         if ((e = cudaMalloc(&c->d_ksk, ksk_len * sizeof(uint64_t))) != cudaSuccess ||
-            (e = cudaMalloc(&c->d_ksk_corr, (c->n + 1) * sizeof(uint64_t))) != cudaSuccess ||
-            (e = cudaMalloc(&c->d_ksk_t, fhs::ksk_tiles_bytes(c))) != cudaSuccess ||
+            (base && (e = cudaMalloc(&c->d_ksk_corr, (c->n + 1) * sizeof(uint64_t))) != cudaSuccess) ||
+            (base && (e = cudaMalloc(&c->d_ksk_t, fhs::ksk_tiles_bytes(c))) != cudaSuccess) ||
             (e = cudaMalloc(&c->d_ksk_u, fhs::ksk_umma_tiles_bytes(c))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_bsk_f, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess ||
             (e = cudaMalloc(&c->d_bsk_w, fhs::bsk_fourier_elems(c) * sizeof(double2))) != cudaSuccess ||
@@ -259,12 +287,14 @@ static int upload_keys_impl(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk
             break;
         }
         if ((rc = fhs::launch_ksk_prepare(c, d_raw, ksk_level_order)) != FHS_OK) break;
-        if ((rc = fhs::launch_ksk_tile(c)) != FHS_OK) break;
+        if (base && (rc = fhs::launch_ksk_corr(c)) != FHS_OK) break;
+        if (base && (rc = fhs::launch_ksk_tile(c)) != FHS_OK) break;
         if ((rc = fhs::launch_ksk_tile_umma(c)) != FHS_OK) break;
         if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "ksk prepare");
             break;
         }
+        if (!base) { cudaFree(c->d_ksk); c->d_ksk = nullptr; }
         if ((e = cudaMemcpyAsync(d_raw, bsk, bsk_len * sizeof(uint64_t), cudaMemcpyHostToDevice,
                                  c->stream)) != cudaSuccess) {
             rc = fhs::cuda_fail(e, "cudaMemcpyAsync(bsk)");
@@ -278,8 +308,7 @@ static int upload_keys_impl(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk
         } else {
             // Fourier BSK rounded once from a double-double transform (bsk_fourier.cu); the f64
             // transform that shares the hot loop's FFT code stays selectable for A/B noise runs
-            const char *xf = getenv("FHS_BSK_XF");
-            const bool f64_only = xf && atoi(xf) == 0;
+            const bool f64_only = c->knobs.bsk_f64 != 0;
             if ((rc = f64_only ? fhs::launch_bsk_transform(c, d_raw) : fhs::launch_bsk_transform_dd(c, d_raw)) != FHS_OK)
                 break;
         }
@@ -306,6 +335,17 @@ int fhs_upload_keys(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ks
 int fhs_upload_keys_fourier(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
                             const double *bsk_fourier, int fourier_convention) {
     return upload_keys_impl(h, p, ksk, ksk_level_order, bsk_fourier, fourier_convention);
+}
+
+// host-pointer entry points: every lut_id must name a row of lut_tables (device-pointer calls cannot be
+// checked without a synchronisation; there the kernels clamp the id)
+static int check_lut_ids(const uint32_t *lut_id, size_t batch, size_t n_luts) {
+    for (size_t b = 0; b < batch; b++)
+        if (lut_id[b] >= n_luts) {
+            fhs::set_error("lut_id[%zu] = %u but there are %zu tables", b, lut_id[b], n_luts);
+            return FHS_ERR_INVALID;
+        }
+    return FHS_OK;
 }
 
 static int check_batch_args(Ctx *c, const void *a, const void *b, const void *t, const void *o,
@@ -337,7 +377,7 @@ int fhs_ks_pbs_batch_dev(fhs_ctx *h, const uint64_t *d_in, const uint32_t *d_lut
     FHS_CUDA(cudaEventRecord(c->ev[0], c->stream));
     if ((rc = fhs::launch_keyswitch(c, d_in, batch, c->d_small)) != FHS_OK) return rc;
     FHS_CUDA(cudaEventRecord(c->ev[1], c->stream));
-    if ((rc = fhs::launch_blind_rotate(c, c->d_small, d_lut_id, d_tables, batch, d_out)) != FHS_OK)
+    if ((rc = fhs::launch_blind_rotate(c, c->d_small, d_lut_id, d_tables, n_luts, batch, d_out)) != FHS_OK)
         return rc;
     FHS_CUDA(cudaEventRecord(c->ev[2], c->stream));
     c->ev_valid[0] = c->ev_valid[1] = true;
@@ -349,6 +389,7 @@ int fhs_ks_pbs_batch(fhs_ctx *h, const uint64_t *lwe_in, const uint32_t *lut_id,
     Ctx *c = reinterpret_cast<Ctx *>(h);
     int rc = check_batch_args(c, lwe_in, lut_id, lut_tables, lwe_out, n_luts, batch);
     if (rc != FHS_OK || batch == 0) return rc;
+    if ((rc = check_lut_ids(lut_id, batch, n_luts)) != FHS_OK) return rc;
     FHS_CUDA(cudaSetDevice(c->device));
     if ((rc = fhs::ensure_capacity(c, batch, n_luts)) != FHS_OK) return rc;
     const size_t w = (size_t)c->big + 1;
@@ -400,7 +441,7 @@ int fhs_ks_pbs_batch(fhs_ctx *h, const uint64_t *lwe_in, const uint32_t *lut_id,
         FHS_CUDA(cudaStreamWaitEvent(c->stream, c->ev_pipe[i], 0));
         uint64_t *small = c->d_small + lo * ((size_t)c->n + 1);
         if ((rc = fhs::launch_keyswitch(c, c->d_in + lo * w, nb, small)) != FHS_OK) return rc;
-        if ((rc = fhs::launch_blind_rotate(c, small, c->d_lut_id + lo, c->d_tables, nb, c->d_out + lo * w)) !=
+        if ((rc = fhs::launch_blind_rotate(c, small, c->d_lut_id + lo, c->d_tables, n_luts, nb, c->d_out + lo * w)) !=
             FHS_OK)
             return rc;
         FHS_CUDA(cudaEventRecord(c->ev_pipe[3 + i], c->stream));
@@ -482,7 +523,7 @@ int fhs_pbs_batch_dev(fhs_ctx *h, const uint64_t *d_small_in, const uint32_t *d_
     if (rc != FHS_OK || batch == 0) return rc;
     FHS_CUDA(cudaSetDevice(c->device));
     FHS_CUDA(cudaEventRecord(c->ev[1], c->stream));
-    if ((rc = fhs::launch_blind_rotate(c, d_small_in, d_lut_id, d_tables, batch, d_out)) != FHS_OK)
+    if ((rc = fhs::launch_blind_rotate(c, d_small_in, d_lut_id, d_tables, n_luts, batch, d_out)) != FHS_OK)
         return rc;
     FHS_CUDA(cudaEventRecord(c->ev[2], c->stream));
     c->ev_valid[0] = false;
@@ -495,6 +536,7 @@ int fhs_pbs_batch(fhs_ctx *h, const uint64_t *small_in, const uint32_t *lut_id,
     Ctx *c = reinterpret_cast<Ctx *>(h);
     int rc = check_batch_args(c, small_in, lut_id, lut_tables, lwe_out, n_luts, batch);
     if (rc != FHS_OK || batch == 0) return rc;
+    if ((rc = check_lut_ids(lut_id, batch, n_luts)) != FHS_OK) return rc;
     FHS_CUDA(cudaSetDevice(c->device));
     if ((rc = fhs::ensure_capacity(c, batch, n_luts)) != FHS_OK) return rc;
     const size_t w = (size_t)c->big + 1;

@@ -33,6 +33,19 @@ struct Ctx {
     double2 *d_bsk_w = nullptr;    // the same values in the layout of blind_rotate_wide.cu
     double2 *d_bsk_x = nullptr;    // ... and in the layout of blind_rotate_pair.cu (one GGSW row per CTA of a pair)
     int pair_limit = -1;           // largest batch of the pair kernel on this device (-1: not queried yet)
+    // Dispatch knobs, read from the environment ONCE per context in fhs_ctx_create (they used to be
+    // process-wide statics initialised from the first context's device).
+    struct Knobs {
+        long wide_limit = 0;       // FHS_BR_WIDE: largest batch of the wide kernel (default 2 per SM; 0 disables)
+        int pair_on = 1;           // FHS_BR_PAIR=0 disables the 2-CTA-cluster kernel
+        int stagger = 4;           // FHS_BR_STAGGER (0 | 3 | 4)
+        int opt = 13;              // FHS_BR_OPT (0 | 1 | 5 | 13)
+        int ks_variant = 3;        // FHS_KS_VARIANT: 3 tcgen05 (default), 2 mma.sync baseline, 1 IMAD baseline
+        int ks_umma_min = 1;       // FHS_KS_UMMA_MIN
+        int ks_mma_min = 1;        // FHS_KS_MMA_MIN
+        int bsk_f64 = 0;           // FHS_BSK_XF=0: plain f64 key transform instead of double-double
+        int ks_baseline_keys = 0;  // key forms of the baseline keyswitch kernels are resident (variant != 3)
+    } knobs;
     double2 *d_twiddle = nullptr;  // [32][33] inter-pass twiddles T[k2][n1]
     // scratch
     uint64_t *d_small = nullptr;   // [cap][n+1] keyswitched ciphertexts
@@ -67,6 +80,7 @@ int cuda_fail(cudaError_t e, const char *what);
 // keyswitch.cu
 int launch_keyswitch(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_small);
 int launch_ksk_prepare(Ctx *c, const uint64_t *d_ksk_raw, int level_order);
+int launch_ksk_corr(Ctx *c);     // offset-correction row of the IMAD baseline kernel only
 // keyswitch_mma.cu
 size_t ksk_tiles_bytes(const Ctx *c);
 int launch_ksk_tile(Ctx *c);
@@ -76,8 +90,10 @@ size_t ksk_umma_tiles_bytes(const Ctx *c);
 int launch_ksk_tile_umma(Ctx *c);
 int launch_keyswitch_umma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_small);
 // blind_rotate.cu
+// every blind-rotation launcher takes n_luts: the kernels clamp lut_id[b] to n_luts - 1, so a bad id in a
+// device-pointer call reads a wrong table instead of memory outside lut_tables
 int launch_blind_rotate(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
-                        const uint64_t *d_tables, size_t batch, uint64_t *d_out);
+                        const uint64_t *d_tables, size_t n_luts, size_t batch, uint64_t *d_out);
 int launch_bsk_transform(Ctx *c, const uint64_t *d_bsk_std);
 // bsk_fourier.cu: the same transform in double-double arithmetic (default; FHS_BSK_XF=0 selects the f64 one)
 int launch_bsk_transform_dd(Ctx *c, const uint64_t *d_bsk_std);
@@ -85,14 +101,14 @@ int launch_bsk_transform_dd(Ctx *c, const uint64_t *d_bsk_std);
 int launch_bsk_import_fourier(Ctx *c, const double2 *d_bsk_fourier, int conj_index);
 // blind_rotate_wide.cu: 4 warps per ciphertext, for levels of at most 2 ciphertexts per SM
 int launch_blind_rotate_wide(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
-                             const uint64_t *d_tables, size_t batch, uint64_t *d_out);
+                             const uint64_t *d_tables, size_t n_luts, size_t batch, uint64_t *d_out);
 int launch_build_lut(Ctx *c, const uint64_t *d_table, uint64_t *d_acc);
 size_t bsk_fourier_elems(const Ctx *c);
 // blind_rotate_pair.cu: one ciphertext per 2-CTA cluster, for levels of at most one ciphertext per two SMs
 int launch_bsk_pair_repack(Ctx *c);
 int blind_rotate_pair_limit(Ctx *c);
 int launch_blind_rotate_pair(Ctx *c, const uint64_t *d_small, const uint32_t *d_lut_id,
-                             const uint64_t *d_tables, size_t batch, uint64_t *d_out);
+                             const uint64_t *d_tables, size_t n_luts, size_t batch, uint64_t *d_out);
 // comm.cu
 void comm_release(Ctx *c);
 

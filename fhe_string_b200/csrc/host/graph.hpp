@@ -9,6 +9,7 @@
 // independent LUT evaluations of an operation land in the same level automatically.
 #pragma once
 #include <array>
+#include <cstdio>
 #include <cstdint>
 #include <map>
 #include <stdexcept>
@@ -38,6 +39,8 @@ struct Node {
     int64_t c;         // plaintext constant (message units)
     int32_t level;     // 0 for inputs
     int32_t lo, hi;    // output value bounds
+    int32_t in_lo = 0, in_hi = 0;  // K_PBS / K_LIN: bounds the builder claims for the linear combination
+    uint8_t signed_in = 0;         // K_PBS: input may be negative (negacyclic LUT use)
 };
 
 using Table = std::array<uint64_t, 16>;
@@ -91,9 +94,19 @@ public:
         }
         int id = lut_fn(f);
         Node n{K_PBS, id, (uint32_t)terms.size(), (uint32_t)e.t.size(), e.c, level_of(e) + 1, out_lo, out_hi};
+        n.in_lo = e.lo; n.in_hi = e.hi; n.signed_in = signed_in ? 1 : 0;
         terms.insert(terms.end(), e.t.begin(), e.t.end());
         nodes.push_back(n);
         if (e.noise > max_input_noise) max_input_noise = e.noise;
+#ifdef FHS_NOISE_DEBUG
+        if (e.noise > 40.f) {
+            fprintf(stderr, "noise %.0f terms %zu lvl %d coefs:", e.noise, e.t.size(), level_of(e) + 1);
+            for (size_t q = 0; q < e.t.size() && q < 12; q++) fprintf(stderr, " %d", e.t[q].coef);
+            fprintf(stderr, " lut:");
+            for (int x = 0; x < 16; x++) fprintf(stderr, "%d,", (int)(f(x) & 31));
+            fprintf(stderr, "\n");
+        }
+#endif
         pbs_count++;
         return leaf((Val)nodes.size() - 1, out_lo, out_hi, 1.f);
     }
@@ -101,6 +114,7 @@ public:
     Val materialize(const Lin &e) {
         if (e.t.size() == 1 && e.t[0].coef == 1 && e.c == 0) return e.t[0].src;
         Node n{K_LIN, -1, (uint32_t)terms.size(), (uint32_t)e.t.size(), e.c, level_of(e), e.lo, e.hi};
+        n.in_lo = e.lo; n.in_hi = e.hi;
         terms.insert(terms.end(), e.t.begin(), e.t.end());
         nodes.push_back(n);
         return (Val)nodes.size() - 1;

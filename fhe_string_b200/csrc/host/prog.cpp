@@ -226,6 +226,21 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
     return FHS_OK;
 }
 
+// Value ranges the builder relied on, per node: in_lo / in_hi bound the linear combination that feeds a
+// PBS (or is materialised), lo / hi bound the node's output, signed_in marks PBS nodes whose input may be
+// negative.  The test suite's clear-text evaluator asserts them, so that a wrong `bounded()`
+// override in the op builders fails at the node where it happens.
+int fhs_prog_export_ranges(const fhs_prog *p, int32_t *in_lo, int32_t *in_hi, int32_t *out_lo, int32_t *out_hi,
+                           uint8_t *signed_in) {
+    if (!p || !in_lo || !in_hi || !out_lo || !out_hi || !signed_in) return FHS_ERR_INVALID;
+    const Graph &g = p->g;
+    for (size_t i = 0; i < g.nodes.size(); i++) {
+        const Node &n = g.nodes[i];
+        in_lo[i] = n.in_lo; in_hi[i] = n.in_hi; out_lo[i] = n.lo; out_hi[i] = n.hi; signed_in[i] = n.signed_in;
+    }
+    return FHS_OK;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------

@@ -18,6 +18,13 @@ namespace fhs_host {
 using Bool = Lin;                // value in {0,1}
 using Rad = std::vector<Lin>;    // little-endian base-4 digits, each in [0,3]
 
+// Largest variance multiplier (units of one PBS output) a one-hot digit sum may reach before its groups
+// are refreshed (round 1: 160).  64 keeps the per-evaluation failure probability of those PBS at 2^-40.0
+// against 2^-40.3 for a single fresh input (DESIGN.md 4 "Noise budget") and still fits the index sum of a
+// 65-char string into 10 groups, i.e. no extra level.  The largest multipliers left in any program are the
+// fan-in-4 sign reduction (85) and the 8-candidate selections of the chunked match scan (129 .. 162).
+constexpr float kMaxLinNoise = 64.f;
+
 struct Ops {
     Graph &g;
     explicit Ops(Graph &g_) : g(g_) {}
@@ -248,7 +255,7 @@ struct Ops {
         return r;
     }
     // Sum of radix values of which AT MOST ONE is non-zero (one-hot selections).  Linear; where the
-    // variance of a digit's sum would exceed 160 PBS outputs the terms are cut into groups below that
+    // variance of a digit's sum would exceed kMaxLinNoise PBS outputs the terms are cut into groups below that
     // bound, every group is refreshed by an identity LUT IN THE SAME LEVEL and the fresh group sums are
     // added (a running sum with refreshes along the way would cost one level per refresh).
     Rad onehot_sum(const std::vector<Rad> &v, size_t nblocks) {
@@ -258,7 +265,7 @@ struct Ops {
             Lin cur = Graph::constant(0);
             for (auto &r : v) {
                 if (r[i].is_const() && r[i].c == 0) continue;
-                if (cur.noise + r[i].noise > 160.f) { groups.push_back(cur); cur = Graph::constant(0); }
+                if (cur.noise + r[i].noise > kMaxLinNoise) { groups.push_back(cur); cur = Graph::constant(0); }
                 cur = bounded(add(cur, r[i]), 0, 3);
             }
             if (groups.empty()) {

@@ -163,6 +163,12 @@ int launch_ksk_prepare(Ctx *c, const uint64_t *d_ksk_raw, int level_order) {
         d_ksk_raw, c->d_ksk, rows, out_w, (int)c->p.ks_level, level_order);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
+    return FHS_OK;
+}
+
+int launch_ksk_corr(Ctx *c) {
+    const size_t rows = (size_t)c->big * c->p.ks_level;
+    const int out_w = (int)c->n + 1;
     ksk_corr_kernel<<<(out_w + 127) / 128, 128, 0, c->stream>>>(c->d_ksk, c->d_ksk_corr, rows, out_w);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
@@ -179,15 +185,13 @@ int launch_keyswitch(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *d_sma
     // FHS_KS_VARIANT: 3 (default) = tcgen05 kernel (keyswitch_umma.cu; faster at every batch size:
     // 0.04 ms for <= 128 ciphertexts, 0.23 ms for 4096) from FHS_KS_UMMA_MIN (default 1) ciphertexts up and
     // the mma.sync kernel (keyswitch_mma.cu, split-K) below; 2 = mma.sync only; 1 = IMAD kernel
-    static int variant = -1;
-    if (variant < 0) { const char *e = getenv("FHS_KS_VARIANT"); variant = e ? atoi(e) : 3; }
-    static int umma_min = -1;
-    if (umma_min < 0) { const char *e = getenv("FHS_KS_UMMA_MIN"); umma_min = e ? atoi(e) : 1; }
-    if (variant == 3 && batch >= (size_t)umma_min) return launch_keyswitch_umma(c, d_in, batch, d_small);
+    // (knobs are per context, read in fhs_ctx_create; the key forms of the two baseline kernels are only
+    // resident when the context was created with FHS_KS_VARIANT != 3 or FHS_KS_UMMA_MIN > 1)
+    const int variant = c->knobs.ks_variant;
+    if (variant == 3 && batch >= (size_t)c->knobs.ks_umma_min) return launch_keyswitch_umma(c, d_in, batch, d_small);
+    if (!c->knobs.ks_baseline_keys) { set_error("baseline keyswitch kernels need FHS_KS_VARIANT set at context creation"); return FHS_ERR_INVALID; }
     const bool use_mma = variant == 2 || variant == 3;
-    static int mma_min = -1;
-    if (mma_min < 0) { const char *e = getenv("FHS_KS_MMA_MIN"); mma_min = e ? atoi(e) : 1; }
-    if (use_mma && batch >= (size_t)mma_min) return launch_keyswitch_mma(c, d_in, batch, d_small);
+    if (use_mma && batch >= (size_t)c->knobs.ks_mma_min) return launch_keyswitch_mma(c, d_in, batch, d_small);
     // tile size: fill the SMs first, then grow tiles up to kKsTb (KSK traffic ~ 1/tile)
     int per = (int)((batch + c->sm_count - 1) / c->sm_count);
     if (per < 1) per = 1;

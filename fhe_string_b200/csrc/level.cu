@@ -165,6 +165,12 @@ int fhs_level(fhs_pool *hp, size_t B, const uint32_t *term_off, const uint32_t *
         return FHS_ERR_INVALID;
     }
     const size_t T = term_off[B];
+    if (T && (!term_idx || !term_coef)) return FHS_ERR_INVALID;
+    for (size_t t = 0; t < T; t++)
+        if (term_idx[t] >= p->capacity) { fhs::set_error("fhs_level: term_idx[%zu] = %u outside the pool (%zu)", t, term_idx[t], p->capacity); return FHS_ERR_INVALID; }
+    if (lut_id)
+        for (size_t b = 0; b < B; b++)
+            if (lut_id[b] >= n_luts) { fhs::set_error("fhs_level: lut_id[%zu] = %u but there are %zu tables", b, lut_id[b], n_luts); return FHS_ERR_INVALID; }
     FHS_CUDA(cudaSetDevice(c->device));
     int rc = fhs::ensure_desc(p, B, T, lut_id ? n_luts : 0);
     if (rc != FHS_OK) return rc;
@@ -231,6 +237,10 @@ int fhs_pool_load_program(fhs_pool *hp, size_t rows, size_t terms, const uint32_
     Pool *p = reinterpret_cast<Pool *>(hp);
     if (!p || !row_off || (terms && (!term_idx || !term_coef)) || (rows && (!const_body || !lut_id)) ||
         (n_luts && !lut_tables)) return FHS_ERR_INVALID;
+    for (size_t t = 0; t < terms; t++)
+        if (term_idx[t] >= p->capacity) { fhs::set_error("fhs_pool_load_program: term_idx[%zu] = %u outside the pool (%zu)", t, term_idx[t], p->capacity); return FHS_ERR_INVALID; }
+    for (size_t r = 0; r < rows; r++)   // rows run with is_pbs = 0 carry lut_id 0
+        if (lut_id[r] >= (n_luts ? n_luts : 1)) { fhs::set_error("fhs_pool_load_program: lut_id[%zu] = %u but there are %zu tables", r, lut_id[r], n_luts); return FHS_ERR_INVALID; }
     Ctx *c = p->ctx;
     FHS_CUDA(cudaSetDevice(c->device));
     cudaStream_t s = c->stream;

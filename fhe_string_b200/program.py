@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "libfhs_string.so")
 _lib = None
 
-HOST_EXPORTS = ["fhs_prog_run_many", "fhs_prog_run_sharded", "fhs_prog_plan", "fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
+HOST_EXPORTS = ["fhs_prog_export_ranges", "fhs_prog_run_many", "fhs_prog_run_sharded", "fhs_prog_plan", "fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
                 "fhs_prog_output_desc", "fhs_prog_export", "fhs_prog_run"]
 
 
@@ -32,6 +32,7 @@ def load_host_library():
     L.fhs_prog_output_desc.argtypes = [vp]
     L.fhs_prog_output_desc.restype = ctypes.c_char_p
     L.fhs_prog_export.argtypes = [vp] * 11
+    L.fhs_prog_export_ranges.argtypes = [vp] * 6
     L.fhs_prog_run.argtypes = [vp, vp, vp, vp, vp]
     L.fhs_prog_run_many.argtypes = [vp, vp, sz, vp, vp, vp]
     L.fhs_prog_run_sharded.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, sz, vp, vp]
@@ -81,6 +82,12 @@ class Program:
                                                "luts", "outputs")])
         if rc != 0:
             raise FhsError("fhs_prog_export failed")
+        r = dict(in_lo=np.zeros(n, np.int32), in_hi=np.zeros(n, np.int32), out_lo=np.zeros(n, np.int32),
+                 out_hi=np.zeros(n, np.int32), signed_in=np.zeros(n, np.uint8))
+        if self.L.fhs_prog_export_ranges(self.h, *[r[k].ctypes.data for k in
+                                                   ("in_lo", "in_hi", "out_lo", "out_hi", "signed_in")]) != 0:
+            raise FhsError("fhs_prog_export_ranges failed")
+        d.update(r)
         return d
 
     def run(self, engine, in_blocks):

@@ -53,6 +53,12 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
                     int64_t *cst, int32_t *level, int32_t *term_src, int32_t *term_coef,
                     uint64_t *luts, int64_t *outputs);
 
+/* Per node: bounds of the linear combination feeding it (in_lo, in_hi), of its output (out_lo, out_hi),
+ * and whether a PBS input may be negative (negacyclic use of the padding bit).  For evaluators that
+ * assert the builder's range claims. */
+int fhs_prog_export_ranges(const fhs_prog *p, int32_t *in_lo, int32_t *in_hi, int32_t *out_lo, int32_t *out_hi,
+                           uint8_t *signed_in);
+
 /* Execute on the GPU: in_blocks [n_inputs][k*N+1] host -> out_blocks [n_outputs][k*N+1] host.
  * Ciphertexts stay in a device pool between levels.  stats[0..3] (may be NULL) = levels run,
  * LUT evaluations, kernels launched, device milliseconds (events around the whole program). */

@@ -10,6 +10,10 @@ from oracle.graph_eval import eval_clear
 from strutil import WS, decode, enc_chars, to_blocks, usize_blocks
 
 _cache = {}
+# Largest variance multiplier (in units of one PBS output, as fhs_prog_info reports it: rounded up) any
+# level program may feed into a PBS.  test_noise_budget_failure_probability turns it into a per-evaluation
+# failure probability (DESIGN.md 4 "Noise budget").
+MAX_NOISE = 163
 
 
 def run(op, strs, pads=None, usizes=(), scalars=(), nbu=4):
@@ -22,8 +26,10 @@ def run(op, strs, pads=None, usizes=(), scalars=(), nbu=4):
     p, ex = _cache[key]
     inputs = [b for c in chars for b in to_blocks(c)] + [b for u in usizes for b in usize_blocks(u, nbu)]
     assert len(inputs) == p.n_inputs
-    assert p.max_noise <= 400, f"{op}: variance multiplier {p.max_noise} fed to a PBS"
-    return decode(p.desc, eval_clear(ex, inputs), nbu)
+    assert p.max_noise <= MAX_NOISE, f"{op}: variance multiplier {p.max_noise} fed to a PBS"
+    out = eval_clear(ex, inputs)        # asserts every range claim of the builder on the way
+    assert all(v <= 3 for v in out), f"{op}: output digit above 3 (clean-block invariant for chained ops): {out}"
+    return decode(p.desc, out, nbu)
 
 
 # (input, pattern, pad) rows in the style of tests/search.rs:15-40, tests/compare.rs:67-110
@@ -291,3 +297,43 @@ def test_ordering_long_strings_first_difference_everywhere():
         assert run("le", [a, b], [44, 41]) == (a <= b), (a, b)
         assert run("gt", [a, b], [44, 41]) == (a > b), (a, b)
         assert run("ge", [a, b], [44, 41]) == (a >= b), (a, b)
+
+
+def test_noise_budget_failure_probability():
+    """The PBS input is  M x (PBS output variance) + keyswitch + modulus-switch noise; a LUT evaluation
+    fails when that exceeds half a box (2^-6 of the torus).  With the oracle's measured PBS output variance
+    (tests/golden/noise_golden.json) and the analytic keyswitch / modulus-switch terms
+    (tests/test_cpu_oracle_first_principles.py checks the former against samples), M = MAX_NOISE must keep the
+    per-evaluation failure probability below tfhe-rs' 2^-40 target for this parameter set."""
+    import json
+    import math
+    import os
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "noise_golden.json")))
+    var_pbs = gold["variance"]
+    n, kN, lwe_std = 742, 2048, 7.069849454709433e-6
+    var_ks = kN * 5 * 66 / 12.0 * lwe_std**2 + (kN / 2.0) * 2.0**-30 / 12.0
+    var_ms = (1.0 / 4096) ** 2 / 12.0 * (1 + n / 2.0)
+    def log2_pfail(m):
+        z = (1.0 / 64) / math.sqrt(m * var_pbs + var_ks + var_ms)
+        return math.log2(math.erfc(z / math.sqrt(2.0)))
+    # fresh input 2^-40.3 (the parameter set itself, tfhe-rs advertises 2^-40 for it); tfhe-rs' bivariate
+    # pack 4x + y (17) 2^-40.2; one-hot digit sums here (<= 64) 2^-40.0; fan-in-4 sign reduction (85)
+    # 2^-39.9; the 8-candidate selections of the chunked match scan in split / replace (<= 163) 2^-39.5
+    assert -40.4 < log2_pfail(1) < -40.2
+    assert log2_pfail(17) < -40.2
+    assert log2_pfail(64) < -39.95
+    assert log2_pfail(MAX_NOISE) < -39.4, log2_pfail(MAX_NOISE)
+    assert log2_pfail(400) > -38.5         # round 1's test bound (400) was well outside the budget
+
+
+def test_noise_multiplier_per_op_class():
+    """Which programs reach which multiplier (64-char operands, 8-char pattern)."""
+    def mx(op, nc, nu=0, sc=()):
+        return Program(op, nc, nu, sc, 4, 4).max_noise
+    for op in ("eq", "contains", "starts_with", "strip_suffix"):
+        assert mx(op, [65, 9]) <= 34
+    for op, nc in (("find", [65, 9]), ("rfind", [65, 9]), ("len", [65]), ("trim", [65]), ("add", [65, 9])):
+        assert mx(op, nc) <= 64
+    assert mx("to_uppercase", [65]) <= 17
+    assert mx("lt", [65, 65]) <= 85
+    assert mx("split", [65, 9]) <= MAX_NOISE and mx("replace", [65, 9, 3], 0, (64,)) <= MAX_NOISE
