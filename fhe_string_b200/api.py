@@ -117,54 +117,151 @@ class ClientKey:
         return "".join(chr(c % 256) for c in chars if c % 256 != 0)
 
 
-class ServerKey:
-    """src/server_key.rs:12-33: key material on the GPU + program cache."""
+class _DevBuf:
+    """A device-resident array of result blocks (fhs_dev_alloc); freed when the last value that slices
+    it goes away.  The first host access downloads the whole array once."""
 
-    def __init__(self, ck, device=0, engine=None):
+    def __init__(self, engine, n_blocks):
+        self.engine, self.n = engine, int(n_blocks)
+        self.ptr = engine.dev_alloc(self.n)
+        self._host = None
+
+    def host(self):
+        if self._host is None:
+            self._host = self.engine.dev_read(self.ptr, self.n)
+        return self._host
+
+    def __del__(self):
+        try:
+            self.engine.dev_free(self.ptr)
+        except Exception:
+            pass
+
+
+class _Ct:
+    """Blocks of one encrypted value: a host array (fresh encryptions), or a slice of a device-resident
+    result (`dev` = (_DevBuf, first block, n blocks)) that is downloaded only when `.blocks` is read --
+    the result of one server operation is the operand of the next without crossing PCIe."""
+
+    def __init__(self, blocks=None, dev=None):
+        self._host = None if blocks is None else np.ascontiguousarray(blocks, dtype=np.uint64)
+        self._dev = dev
+        self.n_blocks = len(self._host) if self._host is not None else int(dev[2])
+
+    @property
+    def blocks(self):
+        if self._host is None:
+            buf, off, n = self._dev
+            self._host = buf.host()[off:off + n]
+        return self._host
+
+    def is_resident(self):
+        return self._dev is not None
+
+    def _operand(self, engine, upload=False):
+        """("dev", pointer, n) when the blocks are resident on this engine's GPU, else ("host", array).
+        upload=True moves a host value to the device at its first use and keeps it there."""
+        if self._dev is not None and not (self._dev[0].engine is engine and engine.h):
+            _ = self.blocks                      # resident elsewhere: go through the host copy
+            self._dev = None
+        if self._dev is None and upload:
+            buf = _DevBuf(engine, self.n_blocks)
+            engine.dev_write(buf.ptr, self._host)
+            buf._host = self._host
+            self._dev = (buf, 0, self.n_blocks)
+        if self._dev is not None:
+            buf, off, n = self._dev
+            return ("dev", buf.ptr + off * engine.big * 8, n)
+        return ("host", self.blocks)
+
+
+class _Out:
+    """Result blocks of one program run, host or device; take(a, b) -> constructor arguments of a value."""
+
+    def __init__(self, host=None, dev=None):
+        self.host, self.dev = host, dev
+
+    def take(self, a, b):
+        if self.dev is not None:
+            return dict(dev=(self.dev, a, b - a))
+        return dict(blocks=self.host[a:b])
+
+    def __len__(self):
+        return self.dev.n if self.dev is not None else len(self.host)
+
+
+class ServerKey:
+    """src/server_key.rs:12-33: key material on the GPU + program cache.
+
+    resident=True (default): results stay in HBM as device-resident arrays and are downloaded when the
+    client first reads them (decrypt); chained operations never cross PCIe.  resident=False returns host
+    arrays like the reference.  With an engine that has a communicator (Engine.comm_init*, one process
+    per GPU) every operation runs sharded: all ranks call it with the same operands."""
+
+    def __init__(self, ck, device=0, engine=None, resident=True):
         if engine is None:
             engine = Engine(device)
             engine.upload_keys(ck.p, ck.ksk(), ck.bsk(), ksk_level_order=0)
         self.engine = engine
         self.num_blocks_char, self.num_blocks_usize = ck.num_blocks_char, ck.num_blocks_usize
         self.max_len = ck.max_len
+        self.resident = resident
+        self.shard_min = 74
         self._progs = {}
+        self._arena = None
         self.last_stats = None
 
     def msg_mod(self):
         return self.engine.p.message_modulus
 
-    def _gather(self, parts):
-        """Operand blocks of one call, assembled in a page-locked arena that lives with the key: the copy
-        is the one np.concatenate would do anyway, but the H2D transfer is then a direct DMA (eq on two
-        65-char strings: 6.2 ms instead of 6.6 ms)."""
+    def _stage(self, parts):
+        """Host operand blocks of one call, copied into a page-locked arena that lives with the engine
+        (fhs_host_alloc): the H2D transfer is then a direct DMA instead of a staged copy."""
         n = sum(len(x) for x in parts)
-        arena = getattr(self, "_arena", None)
-        if arena is None or arena.shape[0] < n:
-            try:
-                import torch
-                t = torch.empty((max(n, 1024), self.engine.big), dtype=torch.int64, pin_memory=True)
-                self._arena_t = t                     # keeps the pinned allocation alive
-                arena = t.numpy().view(np.uint64)
-            except Exception:                         # no torch / pinning refused: pageable memory still works
-                arena = np.empty((max(n, 1024), self.engine.big), dtype=np.uint64)
-            self._arena = arena
-        o = 0
+        if self._arena is None or self._arena.shape[0] < n:
+            self._arena = self.engine.pinned_blocks(max(2 * n, 1024))
+        out, o = [], 0
         for x in parts:
-            arena[o:o + len(x)] = x
+            self._arena[o:o + len(x)] = x
+            out.append(self._arena[o:o + len(x)])
             o += len(x)
-        return arena[:n]
+        return out
 
-    def run(self, op, strings=(), usizes=(), scalars=()):
-        key = (op, tuple(s.n_chars for s in strings), len(usizes), tuple(scalars))
+    def program(self, op, n_chars=(), n_usize=0, scalars=()):
+        key = (op, tuple(n_chars), int(n_usize), tuple(scalars))
         p = self._progs.get(key)
         if p is None:
-            p = Program(op, [s.n_chars for s in strings], len(usizes), scalars, self.num_blocks_char,
-                        self.num_blocks_usize)
+            p = Program(op, list(n_chars), n_usize, scalars, self.num_blocks_char, self.num_blocks_usize)
             self._progs[key] = p
-        parts = [s.blocks for s in strings] + [u.blocks for u in usizes]
-        inb = self._gather(parts) if parts else np.zeros((0, self.engine.big), np.uint64)
-        out, self.last_stats = p.run(self.engine, inb)
+        return p
+
+    def execute(self, p, values):
+        """Run program p on encrypted values (anything with `_operand`), in order."""
+        eng = self.engine
+        raw = [v._operand(eng, upload=self.resident) for v in values]
+        staged = iter(self._stage([o[1] for o in raw if o[0] == "host"]))
+        ops = []
+        for o in raw:
+            if o[0] == "host":
+                ops.append(("host", next(staged)))
+            elif ops and ops[-1][0] == "dev" and ops[-1][1] + ops[-1][2] * eng.big * 8 == o[1]:
+                ops[-1] = ("dev", ops[-1][1], ops[-1][2] + o[2])     # adjacent slices of one result: one copy
+            else:
+                ops.append(o)
+        rank, world = eng.comm if eng.comm else (0, 1)
+        if self.resident:
+            buf = _DevBuf(eng, p.n_outputs)
+            self.last_stats = p.run_ex(eng, ops, out_dev=buf.ptr, rank=rank, world=world, shard_min=self.shard_min)
+            out = _Out(dev=buf)
+        else:
+            host = np.empty((p.n_outputs, eng.big), dtype=np.uint64)
+            self.last_stats = p.run_ex(eng, ops, out_host=host, rank=rank, world=world, shard_min=self.shard_min)
+            out = _Out(host=host)
         return _wrap(p.desc, out, self.num_blocks_usize)
+
+    def run(self, op, strings=(), usizes=(), scalars=()):
+        p = self.program(op, [s.n_chars for s in strings], len(usizes), scalars)
+        return self.execute(p, list(strings) + list(usizes))
 
 
 def generate_keys(l=255, seed=0, device=0):
@@ -173,18 +270,12 @@ def generate_keys(l=255, seed=0, device=0):
     return ck, ServerKey(ck, device)
 
 
-class BooleanBlock:
-    def __init__(self, blocks):
-        self.blocks = blocks
-
+class BooleanBlock(_Ct):
     def decrypt(self, k):
         return k.decrypt_bool(self)
 
 
-class FheUsize:
-    def __init__(self, blocks):
-        self.blocks = blocks
-
+class FheUsize(_Ct):
     def decrypt(self, k):
         return k.decrypt_usize(self)
 
@@ -209,21 +300,15 @@ class FheStringSliceVector:
     def __init__(self, s, entries):
         self.s, self.v = s, entries
 
-    def _blocks(self):
-        parts = [self.s.blocks]
+    def _values(self):
+        vals = [self.s]
         for is_some, start, end in self.v:
-            parts += [is_some.blocks, start.blocks, end.blocks]
-        return np.concatenate(parts)
+            vals += [is_some, start, end]
+        return vals
 
     def _run(self, k, op, extra=()):
-        key = (op, self.s.n_chars, len(self.v))
-        p = k._progs.get(key)
-        if p is None:
-            p = Program(op, [self.s.n_chars], 0, (len(self.v),), k.num_blocks_char, k.num_blocks_usize)
-            k._progs[key] = p
-        inb = np.concatenate([self._blocks()] + [e.blocks for e in extra])
-        out, k.last_stats = p.run(k.engine, inb)
-        return _wrap(p.desc, out, k.num_blocks_usize)
+        p = k.program(op, [self.s.n_chars], 0, (len(self.v),))
+        return k.execute(p, self._values() + list(extra))
 
     def len(self, k):
         """split.rs:32: number of substrings (encrypted)."""
@@ -244,39 +329,40 @@ class FheStringSliceVector:
 
 
 def _wrap(desc, out, nbu):
+    t = out.take
     if desc == "bool":
-        return BooleanBlock(out[:1])
+        return BooleanBlock(**t(0, 1))
     if desc == "usize":
-        return FheUsize(out[:nbu])
+        return FheUsize(**t(0, nbu))
     if desc.startswith("str:"):
-        return FheString(out)
+        return FheString(**t(0, len(out)))
     if desc == "opt_usize":
-        return FheOption(BooleanBlock(out[:1]), FheUsize(out[1:1 + nbu]))
+        return FheOption(BooleanBlock(**t(0, 1)), FheUsize(**t(1, 1 + nbu)))
     if desc.startswith("opt_str:"):
-        return FheOption(BooleanBlock(out[:1]), FheString(out[1:]))
+        return FheOption(BooleanBlock(**t(0, 1)), FheString(**t(1, len(out))))
     if desc.startswith("opt_pair:"):
         _, n1, _n2 = desc.split(":")
         n1 = int(n1) * 4
-        return FheOption(BooleanBlock(out[:1]), (FheString(out[1:1 + n1]), FheString(out[1 + n1:])))
+        return FheOption(BooleanBlock(**t(0, 1)), (FheString(**t(1, 1 + n1)), FheString(**t(1 + n1, len(out)))))
     if desc.startswith("slices:"):
         _, n_entries, _, n_chars = desc.split(":")
         p = 4 * int(n_chars)
-        s = FheString(out[:p])
+        s = FheString(**t(0, p))
         ents = []
         for _ in range(int(n_entries)):
-            ents.append((BooleanBlock(out[p:p + 1]), FheUsize(out[p + 1:p + 1 + nbu]),
-                         FheUsize(out[p + 1 + nbu:p + 1 + 2 * nbu])))
+            ents.append((BooleanBlock(**t(p, p + 1)), FheUsize(**t(p + 1, p + 1 + nbu)),
+                         FheUsize(**t(p + 1 + nbu, p + 1 + 2 * nbu))))
             p += 1 + 2 * nbu
         return FheStringSliceVector(s, ents)
     raise ValueError(desc)
 
 
-class FheString:
+class FheString(_Ct):
     """mod.rs:43-47: Vec<FheAsciiChar>, 0-terminated; blocks = [n_chars * 4][2049] u64."""
 
-    def __init__(self, blocks):
-        self.blocks = np.ascontiguousarray(blocks, dtype=np.uint64)
-        self.n_chars = len(self.blocks) // 4
+    def __init__(self, blocks=None, dev=None):
+        super().__init__(blocks, dev)
+        self.n_chars = self.n_blocks // 4
 
     def decrypt(self, k):
         return k.decrypt_str(self)

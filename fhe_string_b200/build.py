@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfhs_cuda.so")
-SOURCES = ["fhs_api.cu", "keyswitch.cu", "keyswitch_mma.cu", "keyswitch_umma.cu", "blind_rotate.cu", "blind_rotate_wide.cu", "blind_rotate_pair.cu", "bsk_fourier.cu", "peaks.cu", "level.cu", "comm.cu"]
+SOURCES = ["fhs_api.cu", "keyswitch.cu", "keyswitch_mma.cu", "keyswitch_umma.cu", "blind_rotate.cu", "blind_rotate_wide.cu", "blind_rotate_pair.cu", "bsk_fourier.cu", "peaks.cu", "level.cu", "comm.cu", "resident.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--fmad=true",

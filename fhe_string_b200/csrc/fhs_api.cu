@@ -173,6 +173,7 @@ void fhs_ctx_destroy(fhs_ctx *h) {
     Ctx *c = reinterpret_cast<Ctx *>(h);
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    fhs::resident_release(c);
     fhs::comm_release(c);
     fhs::free_keys(c);
     cudaFree(c->d_twiddle);

@@ -65,6 +65,7 @@ struct Ctx {
     bool attr_br = false, attr_brw = false, attr_ks = false, attr_ksu = false;
     // comm.cu: NCCL communicator of this rank (one process per GPU); null on single-GPU contexts
     void *nccl_comm = nullptr;
+    void *resident = nullptr;      // resident.cu: attachment cache, device timer (created on first use)
     int comm_rank = 0, comm_world = 1;
 };
 
@@ -111,5 +112,7 @@ int launch_blind_rotate_pair(Ctx *c, const uint64_t *d_small, const uint32_t *d_
                              const uint64_t *d_tables, size_t n_luts, size_t batch, uint64_t *d_out);
 // comm.cu
 void comm_release(Ctx *c);
+// resident.cu: runs the destructors of everything cached on the context (before its memory goes away)
+void resident_release(Ctx *c);
 
 }  // namespace fhs

@@ -1,6 +1,9 @@
 // fhs_prog: build / export / run level programs (include/fhs_string.h).
+#include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -9,7 +12,10 @@
 
 using namespace fhs_host;
 
+static std::atomic<uint64_t> g_prog_serial{1};
+
 struct fhs_prog {
+    const uint64_t serial = g_prog_serial++;   // owner id of this program's cached executions (fhs_ctx_cache_*)
     Graph g;
     std::vector<int64_t> outputs;  // node id, or -1-c for a clear constant c
     std::string desc;
@@ -192,7 +198,11 @@ int fhs_prog_build(const char *op, const uint32_t *n_chars, size_t n_strings, si
     return FHS_OK;
 }
 
-void fhs_prog_destroy(fhs_prog *p) { delete p; }
+void fhs_prog_destroy(fhs_prog *p) {
+    if (!p) return;
+    fhs_cache_drop_owner(p->serial);   // pools / staging parked on any live context
+    delete p;
+}
 
 const char *fhs_host_last_error(void) { return g_host_err.c_str(); }
 
@@ -245,7 +255,6 @@ int fhs_prog_export_ranges(const fhs_prog *p, int32_t *in_lo, int32_t *in_hi, in
 
 // ------------------------------------------------------------------------------------------------
 // Executor: level by level on a device-resident pool (fhs_pool / fhs_level of include/fhs_cuda.h).
-#include <chrono>
 
 // Slice of a level of B evaluations owned by `rank`.  A level of at most shard_min evaluations (74 =
 // one wave of the pair blind-rotation kernel, 1.7 ms however few ciphertexts it has) is computed
@@ -278,22 +287,32 @@ extern "C" int fhs_prog_plan(const fhs_prog *p, int rank, int world, size_t shar
     return FHS_OK;
 }
 
-extern "C" int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks,
-                            uint64_t *out_blocks, double stats[4]) {
-    return fhs_prog_run_sharded(p, ctx, in_blocks, out_blocks, stats, 0, 1, 0, nullptr, nullptr);
-}
+// Execution state of one program on one context (and one rank / world / shard threshold): the level
+// plan, the device pool with the descriptors of every level resident, and page-locked staging buffers.
+// Built at the first call and parked in the context's attachment cache (fhs_ctx_cache_*), so that every
+// later call of the same operation shape is transfers + kernel launches only: no re-planning, no pool
+// allocation, no descriptor upload (round 1 redid all three per call).
+namespace {
 
-extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks,
-                                    uint64_t *out_blocks, double stats[4], int rank, int world,
-                                    size_t shard_min, fhs_allgather_fn allgather, void *user) {
-    if (!p || !ctx || (!in_blocks && p->n_inputs) || !out_blocks) return FHS_ERR_INVALID;
-    if (world < 1 || rank < 0 || rank >= world) return FHS_ERR_INVALID;
-    if (world > 1 && !allgather) {
-        // no callback: the context's own NCCL communicator (fhs_comm_init) must match rank / world
-        int cr = -1, cw = 0;
-        if (fhs_comm_info(ctx, &cr, &cw) != FHS_OK || cr != rank || cw != world) return FHS_ERR_COMM;
+struct Grp { size_t row0, rows, out_base, per, lo, hi; bool is_pbs; };
+
+struct Exec {
+    fhs_ctx *ctx = nullptr;
+    fhs_pool *pool = nullptr;
+    std::vector<Grp> groups;
+    Grp OG{};
+    size_t n_inputs = 0, n_out = 0, n_pbs = 0, n_levels = 0, n_sharded = 0, width = 0, slots = 0;
+    uint64_t *h_in = nullptr, *h_out = nullptr;   // page-locked staging for pageable caller buffers
+    ~Exec() {
+        if (pool) fhs_pool_destroy(pool);
+        if (h_in) fhs_host_free(ctx, h_in);
+        if (h_out) fhs_host_free(ctx, h_out);
     }
-    if (shard_min == 0) shard_min = 74;
+};
+
+void exec_dtor(void *e) { delete static_cast<Exec *>(e); }
+
+int build_exec(const fhs_prog *p, fhs_ctx *ctx, int rank, int world, size_t shard_min, Exec **out) {
     const Graph &g = p->g;
     fhs_params prm;
     int rc = fhs_ctx_get_params(ctx, &prm);
@@ -302,8 +321,6 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
     const uint64_t delta = (1ull << 63) / ((uint64_t)prm.message_modulus * prm.carry_modulus);
     const size_t N = g.nodes.size();
     const int D = g.depth();
-    auto t_start = std::chrono::steady_clock::now();
-    // ---- plan: slots and descriptor rows of every group, in execution order (host only) ----
     // slots: inputs first, then per level the PBS nodes, then the linear outputs of that level,
     // finally the program outputs gathered into consecutive slots (one read-back at the end)
     std::vector<std::vector<int32_t>> pbs_at(D + 1), lin_at(D + 1);
@@ -316,12 +333,14 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
     for (size_t i = 0; i < N; i++)
         if (g.nodes[i].kind == K_INPUT) slot[i] = (uint32_t)next++;
     if (next != p->n_inputs) return FHS_ERR_INVALID;
-    struct Grp { size_t row0, rows, out_base, per, lo, hi; bool is_pbs; };
-    std::vector<Grp> groups;
+    std::unique_ptr<Exec> E(new Exec());
+    E->ctx = ctx;
+    E->n_inputs = p->n_inputs;
+    E->width = width;
     std::vector<uint32_t> off{0}, idx, lut;
     std::vector<int32_t> coef;
     std::vector<uint64_t> cst;
-    size_t max_rows = 1, n_pbs = 0, n_levels = 0;
+    size_t max_rows = 1;
     auto plan_group = [&](const std::vector<int32_t> &ids, bool is_pbs) {
         if (ids.empty()) return;
         Grp G{cst.size(), ids.size(), next, 0, 0, ids.size(), is_pbs};
@@ -339,16 +358,18 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
         if (is_pbs) {
             level_slice(ids.size(), rank, world, shard_min, &G.per, &G.lo, &G.hi);
             max_rows = std::max(max_rows, G.hi - G.lo);
-            n_pbs += ids.size();
-            n_levels++;
+            E->n_pbs += ids.size();
+            E->n_levels++;
+            if (G.per) E->n_sharded++;
         }
         next += G.per ? G.per * (size_t)world : ids.size();   // sharded levels are padded to per * world
-        groups.push_back(G);
+        E->groups.push_back(G);
     };
     for (int l = 0; l <= D; l++) { plan_group(pbs_at[l], true); plan_group(lin_at[l], false); }
     // output gather group: identity rows (or clear constants as trivial ciphertexts)
     const size_t n_out = p->outputs.size();
-    Grp OG{cst.size(), n_out, next, 0, 0, n_out, false};
+    E->n_out = n_out;
+    E->OG = Grp{cst.size(), n_out, next, 0, 0, n_out, false};
     for (size_t k = 0; k < n_out; k++) {
         if (p->outputs[k] >= 0) {
             idx.push_back(slot[p->outputs[k]]);
@@ -361,17 +382,97 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
         lut.push_back(0u);
     }
     next += n_out;
+    E->slots = next ? next : 1;
     std::vector<uint64_t> tables(g.luts.size() * 16);
     for (size_t i = 0; i < g.luts.size(); i++) memcpy(&tables[16 * i], g.luts[i].data(), 16 * sizeof(uint64_t));
+    if ((rc = fhs_pool_create(ctx, E->slots, &E->pool)) != FHS_OK) return rc;
+    if ((rc = fhs_pool_load_program(E->pool, cst.size(), idx.size(), off.data(), idx.data(), coef.data(), cst.data(),
+                                    lut.data(), tables.data(), g.luts.size(), max_rows)) != FHS_OK) return rc;
+    *out = E.release();
+    return FHS_OK;
+}
 
-    fhs_pool *pool = nullptr;
-    if ((rc = fhs_pool_create(ctx, next ? next : 1, &pool)) != FHS_OK) return rc;
+// staging buffers are made on first need (callers that pass page-locked or device memory never need them)
+int stage_buf(Exec *E, uint64_t **buf, size_t blocks) {
+    if (*buf) return FHS_OK;
+    void *q = nullptr;
+    int rc = fhs_host_alloc(E->ctx, (blocks ? blocks : 1) * E->width * sizeof(uint64_t), &q);
+    if (rc == FHS_OK) *buf = static_cast<uint64_t *>(q);
+    return rc;
+}
+
+}  // namespace
+
+extern "C" int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks,
+                            uint64_t *out_blocks, double stats[4]) {
+    return fhs_prog_run_sharded(p, ctx, in_blocks, out_blocks, stats, 0, 1, 0, nullptr, nullptr);
+}
+
+extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks,
+                                    uint64_t *out_blocks, double stats[4], int rank, int world,
+                                    size_t shard_min, fhs_allgather_fn allgather, void *user) {
+    if (!p || !ctx || (!in_blocks && p->n_inputs) || !out_blocks) return FHS_ERR_INVALID;
+    fhs_operand op{in_blocks, nullptr, p->n_inputs};
+    double st[8];
+    int rc = fhs_prog_run_ex(p, ctx, &op, p->n_inputs ? 1 : 0, out_blocks, nullptr, st, rank, world, shard_min, allgather, user);
+    if (stats) { stats[0] = st[0]; stats[1] = st[1]; stats[2] = st[2]; stats[3] = st[3]; }
+    return rc;
+}
+
+extern "C" int fhs_prog_run_ex(const fhs_prog *p, fhs_ctx *ctx, const fhs_operand *ops, size_t n_ops,
+                               uint64_t *out_host, uint64_t *out_dev, double stats[8], int rank, int world,
+                               size_t shard_min, fhs_allgather_fn allgather, void *user) {
+    if (!p || !ctx || (!ops && n_ops)) return FHS_ERR_INVALID;
+    if (world < 1 || rank < 0 || rank >= world) return FHS_ERR_INVALID;
+    if (world > 1 && !allgather) {
+        // no callback: the context's own NCCL communicator (fhs_comm_init) must match rank / world
+        int cr = -1, cw = 0;
+        if (fhs_comm_info(ctx, &cr, &cw) != FHS_OK || cr != rank || cw != world) return FHS_ERR_COMM;
+    }
+    if (shard_min == 0) shard_min = 74;
+    size_t given = 0;
+    for (size_t i = 0; i < n_ops; i++) {
+        if (ops[i].n_blocks && !ops[i].host && !ops[i].dev) return FHS_ERR_INVALID;
+        given += ops[i].n_blocks;
+    }
+    if (given != p->n_inputs) { g_host_err = "operand blocks do not add up to the program's inputs"; return FHS_ERR_INVALID; }
+    auto t_start = std::chrono::steady_clock::now();
+    // ---- cached execution state ----
+    const uint64_t key[4] = {p->serial, (uint64_t)rank, (uint64_t)world, (uint64_t)shard_min};
+    void *obj = nullptr;
+    int rc = fhs_ctx_cache_get(ctx, key, &obj);
+    if (rc != FHS_OK) return rc;
+    Exec *E = static_cast<Exec *>(obj);
+    const bool cached = E != nullptr;
+    if (!E) {
+        if ((rc = build_exec(p, ctx, rank, world, shard_min, &E)) != FHS_OK) { delete E; return rc; }
+        if ((rc = fhs_ctx_cache_put(ctx, key, E, exec_dtor, E->slots * E->width * sizeof(uint64_t))) != FHS_OK) { delete E; return rc; }
+    }
+    const double plan_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
+    const size_t width = E->width, n_out = E->n_out;
     const uint64_t launches0 = fhs_launch_count(ctx);
+    fhs_pool *pool = E->pool;
+    bool timed = fhs_ctx_timer_start(ctx) == FHS_OK;
     do {
-        if ((rc = fhs_pool_load_program(pool, cst.size(), idx.size(), off.data(), idx.data(), coef.data(),
-                                        cst.data(), lut.data(), tables.data(), g.luts.size(), max_rows)) != FHS_OK) break;
-        if (p->n_inputs && (rc = fhs_pool_write(pool, 0, p->n_inputs, in_blocks)) != FHS_OK) break;
-        for (const Grp &G : groups) {
+        // ---- operands: device arrays are copied on the device; host arrays go by DMA straight from
+        // page-locked memory, pageable ones through the page-locked staging buffer ----
+        size_t slot = 0;
+        for (size_t i = 0; i < n_ops && rc == FHS_OK; i++) {
+            const size_t nb = ops[i].n_blocks;
+            if (!nb) continue;
+            if (ops[i].dev) {
+                rc = fhs_pool_copy_in(pool, slot, nb, ops[i].dev);
+            } else if (fhs_host_is_pinned(ops[i].host)) {
+                rc = fhs_pool_enqueue_write(pool, slot, nb, ops[i].host);
+            } else {
+                if ((rc = stage_buf(E, &E->h_in, E->n_inputs)) != FHS_OK) break;
+                memcpy(E->h_in + slot * width, ops[i].host, nb * width * sizeof(uint64_t));
+                rc = fhs_pool_enqueue_write(pool, slot, nb, E->h_in + slot * width);
+            }
+            slot += nb;
+        }
+        if (rc != FHS_OK) break;
+        for (const Grp &G : E->groups) {
             if (G.hi > G.lo && (rc = fhs_level_run(pool, G.row0 + G.lo, G.hi - G.lo, G.is_pbs ? 1 : 0, G.out_base + G.lo)) != FHS_OK) break;
             if (G.per) {  // exchange result blocks: rank q owns [out_base + q*per, out_base + (q+1)*per)
                 uint64_t *base = fhs_pool_device_ptr(pool) + G.out_base * width;
@@ -387,18 +488,35 @@ extern "C" int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint6
         }
         if (rc != FHS_OK) break;
         if (n_out) {
-            if ((rc = fhs_level_run(pool, OG.row0, n_out, 0, OG.out_base)) != FHS_OK) break;
-            rc = fhs_pool_read(pool, OG.out_base, n_out, out_blocks);
+            if ((rc = fhs_level_run(pool, E->OG.row0, n_out, 0, E->OG.out_base)) != FHS_OK) break;
+            if (out_dev && (rc = fhs_pool_copy_out(pool, E->OG.out_base, n_out, out_dev)) != FHS_OK) break;
+        }
+        if (timed) fhs_ctx_timer_stop(ctx);
+        if (n_out && out_host) {
+            if (fhs_host_is_pinned(out_host)) {
+                rc = fhs_pool_enqueue_read(pool, E->OG.out_base, n_out, out_host);
+            } else {
+                if ((rc = stage_buf(E, &E->h_out, n_out)) != FHS_OK) break;
+                if ((rc = fhs_pool_enqueue_read(pool, E->OG.out_base, n_out, E->h_out)) != FHS_OK) break;
+                if ((rc = fhs_ctx_synchronize(ctx)) != FHS_OK) break;
+                memcpy(out_host, E->h_out, n_out * width * sizeof(uint64_t));
+            }
         }
     } while (0);
-    fhs_ctx_synchronize(ctx);
+    const int src = fhs_ctx_synchronize(ctx);   // operands (caller memory) and results are settled on return
+    if (rc == FHS_OK) rc = src;
     if (stats) {
-        stats[0] = (double)n_levels;
-        stats[1] = (double)n_pbs;
+        float dev_ms = 0.f;
+        if (!(timed && rc == FHS_OK && fhs_ctx_timer_ms(ctx, &dev_ms) == FHS_OK)) dev_ms = -1.f;
+        stats[0] = (double)E->n_levels;
+        stats[1] = (double)E->n_pbs;
         stats[2] = (double)(fhs_launch_count(ctx) - launches0);
         stats[3] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
+        stats[4] = (double)dev_ms;
+        stats[5] = plan_ms;
+        stats[6] = (double)E->n_sharded;
+        stats[7] = cached ? 1.0 : 0.0;
     }
-    fhs_pool_destroy(pool);
     return rc;
 }
 

@@ -151,6 +151,49 @@ int fhs_pool_read(fhs_pool *hp, size_t slot, size_t n, uint64_t *host_blocks) {
     return FHS_OK;
 }
 
+// Un-synchronised transfers on the context's stream, for callers that own the host buffer until their
+// next fhs_ctx_synchronize (the cached executions of libfhs_string: page-locked staging), and device to
+// device copies between a pool and a resident ciphertext array (fhs_dev_alloc).
+int fhs_pool_enqueue_write(fhs_pool *hp, size_t slot, size_t n, const uint64_t *host_blocks) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || (!host_blocks && n) || slot + n > p->capacity) { fhs::set_error("pool write out of range"); return FHS_ERR_INVALID; }
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    const size_t w = (size_t)c->big + 1;
+    FHS_CUDA(cudaMemcpyAsync(p->d + slot * w, host_blocks, n * w * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+    return FHS_OK;
+}
+
+int fhs_pool_enqueue_read(fhs_pool *hp, size_t slot, size_t n, uint64_t *host_blocks) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || (!host_blocks && n) || slot + n > p->capacity) { fhs::set_error("pool read out of range"); return FHS_ERR_INVALID; }
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    const size_t w = (size_t)c->big + 1;
+    FHS_CUDA(cudaMemcpyAsync(host_blocks, p->d + slot * w, n * w * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+    return FHS_OK;
+}
+
+int fhs_pool_copy_in(fhs_pool *hp, size_t slot, size_t n, const uint64_t *d_src) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || (!d_src && n) || slot + n > p->capacity) { fhs::set_error("pool copy out of range"); return FHS_ERR_INVALID; }
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    const size_t w = (size_t)c->big + 1;
+    FHS_CUDA(cudaMemcpyAsync(p->d + slot * w, d_src, n * w * sizeof(uint64_t), cudaMemcpyDeviceToDevice, c->stream));
+    return FHS_OK;
+}
+
+int fhs_pool_copy_out(fhs_pool *hp, size_t slot, size_t n, uint64_t *d_dst) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || (!d_dst && n) || slot + n > p->capacity) { fhs::set_error("pool copy out of range"); return FHS_ERR_INVALID; }
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    const size_t w = (size_t)c->big + 1;
+    FHS_CUDA(cudaMemcpyAsync(d_dst, p->d + slot * w, n * w * sizeof(uint64_t), cudaMemcpyDeviceToDevice, c->stream));
+    return FHS_OK;
+}
+
 // One level: B linear combinations of pool blocks; if lut_id != NULL each is keyswitched and
 // bootstrapped through lut_tables[lut_id[b]]; results land in pool slots [out_slot, out_slot + B).
 int fhs_level(fhs_pool *hp, size_t B, const uint32_t *term_off, const uint32_t *term_idx,

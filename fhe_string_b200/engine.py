@@ -35,6 +35,10 @@ EXPORTS = [
     "fhs_ks_pbs_batch_dev", "fhs_keyswitch_batch", "fhs_keyswitch_batch_dev", "fhs_build_lut",
     "fhs_pbs_batch", "fhs_pbs_batch_dev", "fhs_last_kernel_ms", "fhs_launch_count",
     "fhs_measure_fp64_tflops",
+    "fhs_pool_enqueue_write", "fhs_pool_enqueue_read", "fhs_pool_copy_in", "fhs_pool_copy_out",
+    "fhs_dev_alloc", "fhs_dev_free", "fhs_dev_write", "fhs_dev_read", "fhs_host_alloc", "fhs_host_free",
+    "fhs_host_is_pinned", "fhs_ctx_cache_get", "fhs_ctx_cache_put", "fhs_cache_drop_owner",
+    "fhs_ctx_cache_stats", "fhs_ctx_cache_limit", "fhs_ctx_timer_start", "fhs_ctx_timer_stop", "fhs_ctx_timer_ms",
 ]
 
 _lib = None
@@ -84,6 +88,17 @@ def load_library():
     L.fhs_launch_count.argtypes = [vp]
     L.fhs_launch_count.restype = ctypes.c_uint64
     L.fhs_measure_fp64_tflops.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
+    L.fhs_dev_alloc.argtypes = [vp, sz, ctypes.POINTER(vp)]
+    L.fhs_dev_free.argtypes = [vp, vp]
+    L.fhs_dev_free.restype = None
+    L.fhs_dev_write.argtypes = [vp, vp, sz, vp]
+    L.fhs_dev_read.argtypes = [vp, vp, sz, vp]
+    L.fhs_host_alloc.argtypes = [vp, sz, ctypes.POINTER(vp)]
+    L.fhs_host_free.argtypes = [vp, vp]
+    L.fhs_host_free.restype = None
+    L.fhs_host_is_pinned.argtypes = [vp]
+    L.fhs_ctx_cache_stats.argtypes = [vp, ctypes.POINTER(sz), ctypes.POINTER(sz)]
+    L.fhs_ctx_cache_limit.argtypes = [vp, sz]
     _lib = L
     return L
 
@@ -118,8 +133,50 @@ class Engine:
 
     def close(self):
         if getattr(self, "h", None):
-            self.L.fhs_ctx_destroy(self.h)
+            for ch in getattr(self, "_pinned", []):
+                self.L.fhs_host_free(self.h, ctypes.c_void_p(ch))
+            self._pinned = []
+            self.L.fhs_ctx_destroy(self.h)    # also frees cached executions and device arrays' allocator
             self.h = None
+
+    # ---- residency: device-resident ciphertext arrays, page-locked host buffers, cache ----
+    def dev_alloc(self, n_blocks):
+        d = ctypes.c_void_p()
+        self._check(self.L.fhs_dev_alloc(self.h, int(n_blocks), ctypes.byref(d)))
+        return int(d.value)
+
+    def dev_free(self, ptr):
+        if getattr(self, "h", None) and ptr:
+            self.L.fhs_dev_free(self.h, ctypes.c_void_p(ptr))
+
+    def dev_write(self, ptr, blocks):
+        blocks = np.ascontiguousarray(blocks, dtype=np.uint64).reshape(-1, self.big)
+        self._check(self.L.fhs_dev_write(self.h, ctypes.c_void_p(ptr), len(blocks), blocks.ctypes.data))
+
+    def dev_read(self, ptr, n_blocks, out=None):
+        if out is None:
+            out = np.empty((n_blocks, self.big), dtype=np.uint64)
+        self._check(self.L.fhs_dev_read(self.h, ctypes.c_void_p(ptr), int(n_blocks), out.ctypes.data))
+        return out
+
+    def pinned_blocks(self, n_blocks):
+        """A page-locked u64 [n_blocks][big] array that lives until close() (operand staging arenas)."""
+        q = ctypes.c_void_p()
+        nbytes = max(1, int(n_blocks)) * self.big * 8
+        self._check(self.L.fhs_host_alloc(self.h, nbytes, ctypes.byref(q)))
+        if not hasattr(self, "_pinned"):
+            self._pinned = []
+        self._pinned.append(int(q.value))
+        buf = (ctypes.c_uint64 * (max(1, int(n_blocks)) * self.big)).from_address(q.value)
+        return np.ctypeslib.as_array(buf).reshape(-1, self.big)
+
+    def cache_stats(self):
+        n, b = ctypes.c_size_t(), ctypes.c_size_t()
+        self._check(self.L.fhs_ctx_cache_stats(self.h, ctypes.byref(n), ctypes.byref(b)))
+        return int(n.value), int(b.value)
+
+    def cache_limit(self, device_bytes):
+        self._check(self.L.fhs_ctx_cache_limit(self.h, int(device_bytes)))
 
     def __del__(self):
         try:

@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "libfhs_string.so")
 _lib = None
 
-HOST_EXPORTS = ["fhs_prog_export_ranges", "fhs_prog_run_many", "fhs_prog_run_sharded", "fhs_prog_plan", "fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
+HOST_EXPORTS = ["fhs_prog_run_ex", "fhs_prog_export_ranges", "fhs_prog_run_many", "fhs_prog_run_sharded", "fhs_prog_plan", "fhs_prog_build", "fhs_prog_destroy", "fhs_host_last_error", "fhs_prog_info",
                 "fhs_prog_output_desc", "fhs_prog_export", "fhs_prog_run"]
 
 
@@ -34,11 +34,27 @@ def load_host_library():
     L.fhs_prog_export.argtypes = [vp] * 11
     L.fhs_prog_export_ranges.argtypes = [vp] * 6
     L.fhs_prog_run.argtypes = [vp, vp, vp, vp, vp]
+    L.fhs_prog_run_ex.argtypes = [vp, vp, vp, sz, vp, vp, vp, ctypes.c_int, ctypes.c_int, sz, vp, vp]
     L.fhs_prog_run_many.argtypes = [vp, vp, sz, vp, vp, vp]
     L.fhs_prog_run_sharded.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, sz, vp, vp]
     L.fhs_prog_plan.argtypes = [vp, ctypes.c_int, ctypes.c_int, sz, vp, sz, ctypes.POINTER(sz)]
     _lib = L
     return L
+
+
+class Operand(ctypes.Structure):
+    """fhs_operand: a piece of a program's input, in host memory or resident on the device."""
+    _fields_ = [("host", ctypes.c_void_p), ("dev", ctypes.c_void_p), ("n_blocks", ctypes.c_size_t)]
+
+
+STAT_KEYS = ("levels", "pbs", "launches", "ms", "device_ms", "plan_ms", "sharded_levels", "cached")
+
+
+def _stats(st):
+    d = dict(levels=int(st[0]), pbs=int(st[1]), launches=int(st[2]), ms=float(st[3]))
+    if len(st) > 4:
+        d.update(device_ms=float(st[4]), plan_ms=float(st[5]), sharded_levels=int(st[6]), cached=bool(st[7]))
+    return d
 
 
 class Program:
@@ -99,6 +115,31 @@ class Program:
         if rc != 0:
             raise FhsError(f"fhs_prog_run({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()}")
         return out, dict(levels=int(stats[0]), pbs=int(stats[1]), launches=int(stats[2]), ms=float(stats[3]))
+
+    def run_ex(self, engine, operands, out_host=None, out_dev=0, rank=0, world=1, shard_min=74):
+        """fhs_prog_run_ex.  operands: list of ("host", ndarray[n][big]) / ("dev", device_ptr, n_blocks);
+        out_host: ndarray [n_outputs][big] or None; out_dev: device pointer or 0.  Cached execution state
+        per (program, engine, rank, world, shard_min).  Multi-rank runs need Engine.comm_init*."""
+        ops = (Operand * max(1, len(operands)))()
+        keep = []
+        for i, o in enumerate(operands):
+            if o[0] == "dev":
+                ops[i].host, ops[i].dev, ops[i].n_blocks = None, o[1], int(o[2])
+            else:
+                a = o[1]
+                if not (a.flags["C_CONTIGUOUS"] and a.dtype == np.uint64):
+                    a = np.ascontiguousarray(a, dtype=np.uint64)
+                keep.append(a)
+                ops[i].host, ops[i].dev, ops[i].n_blocks = a.ctypes.data, None, a.size // engine.big
+        stats = np.zeros(8, dtype=np.float64)
+        rc = self.L.fhs_prog_run_ex(self.h, engine.h, ctypes.addressof(ops), len(operands),
+                                    out_host.ctypes.data if out_host is not None else None,
+                                    ctypes.c_void_p(out_dev) if out_dev else None, stats.ctypes.data,
+                                    int(rank), int(world), int(shard_min), None, None)
+        if rc != 0:
+            raise FhsError(f"fhs_prog_run_ex({self.op}) failed ({rc}): {engine.L.fhs_last_error().decode()} "
+                           f"{self.L.fhs_host_last_error().decode()}")
+        return _stats(stats)
 
     def run_many(self, engine, in_blocks):
         """M independent instances: in_blocks u64 [M][n_inputs][2049] -> ([M][n_outputs][2049], stats).

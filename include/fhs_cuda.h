@@ -172,6 +172,42 @@ int fhs_pool_load_program(fhs_pool *pool, size_t rows, size_t terms, const uint3
                           size_t max_level_rows);
 int fhs_level_run(fhs_pool *pool, size_t row_lo, size_t B, int is_pbs, size_t out_slot);
 
+/* ---- resident operands and cached executions (SURVEY.md 8b "ciphertext-pool handles") ---------
+ * Un-synchronised pool transfers on the context's stream (the caller keeps the host buffer alive and
+ * unchanged until its next fhs_ctx_synchronize) and device-to-device copies between a pool and a
+ * resident ciphertext array. */
+int fhs_pool_enqueue_write(fhs_pool *pool, size_t slot, size_t n, const uint64_t *host_blocks);
+int fhs_pool_enqueue_read(fhs_pool *pool, size_t slot, size_t n, uint64_t *host_blocks);
+int fhs_pool_copy_in(fhs_pool *pool, size_t slot, size_t n, const uint64_t *d_src);
+int fhs_pool_copy_out(fhs_pool *pool, size_t slot, size_t n, uint64_t *d_dst);
+/* Device-resident ciphertext arrays [n_blocks][k*N+1] (stream-ordered allocation on the context's
+ * stream): the result of one operation is the operand of the next without crossing PCIe.  Replaces the
+ * host-side Vec<Ciphertext> the reference passes between its ops (src/ciphertext/mod.rs:43-47). */
+int fhs_dev_alloc(fhs_ctx *ctx, size_t n_blocks, uint64_t **d_out);
+void fhs_dev_free(fhs_ctx *ctx, uint64_t *d);
+int fhs_dev_write(fhs_ctx *ctx, uint64_t *d, size_t n_blocks, const uint64_t *host_blocks);   /* synchronous */
+int fhs_dev_read(fhs_ctx *ctx, const uint64_t *d, size_t n_blocks, uint64_t *host_blocks);    /* synchronous */
+/* Page-locked host memory for operand / result staging (direct DMA instead of a staged copy). */
+int fhs_host_alloc(fhs_ctx *ctx, size_t bytes, void **out);
+void fhs_host_free(fhs_ctx *ctx, void *p);
+int fhs_host_is_pinned(const void *p);
+/* Attachment cache of a context: a caller (the level scheduler, fhs_string.h) parks per-program state
+ * that lives on this GPU -- the planned pool with its resident level descriptors -- under a 4-word key
+ * (key[0] = owner id).  Entries are destroyed (dtor) with the context, when their owner goes away
+ * (fhs_cache_drop_owner, every live context) or least-recently-used first when the sum of device_bytes
+ * exceeds the budget (default 16 GiB, FHS_CACHE_BYTES / fhs_ctx_cache_limit). */
+typedef void (*fhs_cache_dtor)(void *obj);
+int fhs_ctx_cache_get(fhs_ctx *ctx, const uint64_t key[4], void **obj);   /* *obj = NULL when absent */
+int fhs_ctx_cache_put(fhs_ctx *ctx, const uint64_t key[4], void *obj, fhs_cache_dtor dtor, size_t device_bytes);
+void fhs_cache_drop_owner(uint64_t owner);
+int fhs_ctx_cache_stats(fhs_ctx *ctx, size_t *entries, size_t *device_bytes);
+int fhs_ctx_cache_limit(fhs_ctx *ctx, size_t device_bytes);
+/* Device timer: CUDA events on the context's stream around whatever is enqueued between start and stop;
+ * fhs_ctx_timer_ms waits for the stop event. */
+int fhs_ctx_timer_start(fhs_ctx *ctx);
+int fhs_ctx_timer_stop(fhs_ctx *ctx);
+int fhs_ctx_timer_ms(fhs_ctx *ctx, float *ms);
+
 /* ---- multi-GPU: one process per GPU, a key replica per GPU ---------------------
  * The path shards over independent LUT evaluations; the only traffic is the server keys once
  * (broadcast) and the result blocks of a level that was split by rank (all-gather).  Both are NCCL

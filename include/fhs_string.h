@@ -23,6 +23,8 @@ extern "C" {
 #endif
 
 typedef struct fhs_prog fhs_prog;
+/* exchange callback of fhs_prog_run_sharded / fhs_prog_run_ex (see there) */
+typedef int (*fhs_allgather_fn)(void *user, uint64_t *device_base, size_t bytes_per_rank);
 
 /* Build the program of operation `op` (the reference method name: "eq", "ne", "lt", "le", "gt",
  * "ge", "eq_ignore_ascii_case", "is_empty", "len", "to_uppercase", "to_lowercase", "contains",
@@ -65,6 +67,22 @@ int fhs_prog_export_ranges(const fhs_prog *p, int32_t *in_lo, int32_t *in_hi, in
 int fhs_prog_run(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks, uint64_t *out_blocks,
                  double stats[4]);
 
+/* General form: operands given piecewise, each piece a HOST array or a DEVICE-resident array
+ * (fhs_dev_alloc, fhs_cuda.h) of n_blocks blocks, concatenated in order to the program's inputs; the
+ * result goes to out_host and / or out_dev (either may be NULL).  Results left on the device feed the
+ * next operation without crossing PCIe (to_uppercase -> contains).  Page-locked host memory
+ * (fhs_host_alloc) is transferred by direct DMA, pageable memory through a page-locked staging buffer.
+ * The planned pool with its resident level descriptors is cached on the context per (program, rank,
+ * world, shard_min): a repeated call is transfers + kernel launches only.  Synchronous: operands and
+ * results are settled when the call returns.
+ * stats[0..7] = levels, LUT evaluations, kernels launched, wall ms of the call, DEVICE ms (events on the
+ * context's stream around operand copies + levels, -1 if unavailable), host planning ms (0.0x when
+ * cached), levels that were split by rank, 1 if the execution state came from the cache. */
+typedef struct { const uint64_t *host; const uint64_t *dev; size_t n_blocks; } fhs_operand;
+int fhs_prog_run_ex(const fhs_prog *p, fhs_ctx *ctx, const fhs_operand *ops, size_t n_ops, uint64_t *out_host,
+                    uint64_t *out_dev, double stats[8], int rank, int world, size_t shard_min,
+                    fhs_allgather_fn allgather, void *user);
+
 /* M independent instances of the same program in one pass (e.g. the 1024 string comparisons of a
  * throughput sweep): in_blocks [M][n_inputs][k*N+1], out_blocks [M][n_outputs][k*N+1].  Every level
  * is evaluated for all instances at once (chunks of <= 32768 LUT evaluations per fhs_level call), so
@@ -83,7 +101,6 @@ int fhs_prog_run_many(const fhs_prog *p, fhs_ctx *ctx, size_t n_instances, const
  * stream through the communicator set up with fhs_comm_init (fhs_cuda.h) -- no host
  * synchronisation between levels, no host framework in the loop; FHS_ERR_COMM if the context has no
  * communicator of this rank / world. */
-typedef int (*fhs_allgather_fn)(void *user, uint64_t *device_base, size_t bytes_per_rank);
 int fhs_prog_run_sharded(const fhs_prog *p, fhs_ctx *ctx, const uint64_t *in_blocks, uint64_t *out_blocks,
                          double stats[4], int rank, int world, size_t shard_min,
                          fhs_allgather_fn allgather, void *user);

@@ -68,3 +68,68 @@ def test_config4_256_char_ops_full_size():
     assert es.replace(sk, ck.encrypt_str(pat), ck.encrypt_str("c"), 256).decrypt(ck) == s.replace(pat, "c")
     assert es.len(sk).decrypt(ck) == 200
     sk.engine.close()
+
+
+def test_resident_results_chain_without_host_copies(keys):
+    """Results stay in HBM (device-resident arrays) and feed the next op; the host copy is made at the first
+    `.blocks` / decrypt.  Same answers as the host-array mode; cached execution state on the second call."""
+    from fhe_string_b200.api import ServerKey
+    ck, sk = keys
+    s = ck.encrypt_str("Hello, B200!", 16)
+    up = s.to_uppercase(sk)
+    assert up.is_resident() and up._host is None                       # nothing downloaded yet
+    st1 = dict(sk.last_stats)
+    hit = up.contains(sk, ck.encrypt_str("B200"))                      # operand straight from device memory
+    assert hit.decrypt(ck) is True
+    assert up.decrypt(ck) == "HELLO, B200!"
+    assert s.to_uppercase(sk).decrypt(ck) == "HELLO, B200!"
+    st2 = sk.last_stats
+    assert st2["cached"] and st2["plan_ms"] < st1["plan_ms"] + 0.5 and st2["device_ms"] > 0
+    assert st2["levels"] == st1["levels"] and st2["pbs"] == st1["pbs"]
+    # split result: 1 + 3 x entries slices of one device array, chained into slices_get
+    sv = s.split(sk, ck.encrypt_str("l"))
+    assert sv.get(sk, ck.encrypt_usize(1)).decrypt(ck) == ""
+    assert sv.decrypt(ck) == "Hello, B200!".split("l")
+    # host-array mode gives the same answers
+    hk = ServerKey(ck, engine=sk.engine, resident=False)
+    up2 = s.to_uppercase(hk)
+    assert not up2.is_resident() and up2.decrypt(ck) == "HELLO, B200!"
+    assert up2.contains(hk, ck.encrypt_str("B200")).decrypt(ck) is True
+    n, nbytes = sk.engine.cache_stats()
+    assert n >= 3 and nbytes > 0
+
+
+def test_execution_cache_follows_program_and_budget(keys):
+    import gc
+    from fhe_string_b200.program import Program
+    ck, sk = keys
+    eng = sk.engine
+    n0, _ = eng.cache_stats()
+    p = Program("to_lowercase", [5], 0, (), 4, 4)
+    cts = ck.encrypt_str("AbCd").blocks
+    out, st = p.run(eng, cts)
+    assert "".join(chr(c) for c in ck._radix(out, 4) if c) == "abcd"
+    assert eng.cache_stats()[0] == n0 + 1
+    out2, st2 = p.run(eng, cts)
+    assert st2["ms"] < st["ms"] + 1.0
+    del p
+    gc.collect()
+    assert eng.cache_stats()[0] == n0                                   # fhs_prog_destroy dropped its entry
+    eng.cache_limit(1)                                                  # 1 byte: everything but the newest goes
+    assert sk.program("is_empty", [3]) is not None
+    ck.encrypt_str("ab").is_empty(sk)
+    assert eng.cache_stats()[0] <= 1
+    eng.cache_limit(16 << 30)
+
+
+def test_bad_lut_id_is_rejected(keys):
+    import numpy as np
+    ck, sk = keys
+    cts = ck.encrypt_blocks([1, 2, 3])
+    tables = np.arange(32, dtype=np.uint64).reshape(2, 16) % 16
+    with pytest.raises(Exception) as e:
+        lut = np.array([0, 1, 2], dtype=np.uint32)                      # 2 is out of range
+        out = np.empty_like(cts)
+        sk.engine._check(sk.engine.L.fhs_ks_pbs_batch(sk.engine.h, cts.ctypes.data, lut.ctypes.data,
+                                                       tables.ctypes.data, 2, 3, out.ctypes.data))
+    assert "lut_id" in str(e.value)
