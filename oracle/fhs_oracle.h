@@ -99,6 +99,10 @@ int orc_ks_pbs_batch(const orc_keyset *ks, const uint64_t *lwe_in, const uint32_
 void orc_decompose(uint64_t x, int base_log, int level, int64_t *digits_out);
 
 int orc_max_threads(void);
+/* 1 for the ORC_FAST build (oracle/Makefile target `fast`): same algorithm, -march=native, SoA radix-4
+ * FFT without permutations, per-thread scratch -- the CPU arm bench.py times; NOT bit-identical to the
+ * portable build the golden vectors pin. */
+int orc_is_fast_build(void);
 
 #ifdef __cplusplus
 }

@@ -132,3 +132,29 @@ def test_noise_golden_matches_live_oracle(keyset):
     assert np.array_equal(keyset.decrypt(out), want)
     var = float(np.var(keyset.phase_error(out, want)))
     assert 0.55 * gold["variance"] < var < 1.6 * gold["variance"], (var, gold["variance"])
+
+
+def test_fast_build_same_algorithm_different_rounding():
+    """oracle/Makefile `fast` (-DORC_FAST -march=native: SoA radix-4 FFT without permutations, per-thread
+    scratch) is the CPU arm bench.py times.  It is the same algorithm: integer tiers bit-identical to the
+    portable build, PBS decrypt-exact with the same noise level, its external product within FFT rounding
+    of the exact integer convolution -- but not bit-identical (summation order, FMA contraction)."""
+    from test_cpu_oracle_first_principles import signed
+    slow, fast = O.Keyset(seed=1), O.Keyset(seed=1, fast=True)
+    assert fast.L.orc_is_fast_build() == 1 and slow.L.orc_is_fast_build() == 0
+    assert np.array_equal(slow.ksk(), fast.ksk()) and np.array_equal(slow.bsk(), fast.bsk())
+    rng = np.random.default_rng(3)
+    msgs = rng.integers(0, 16, 24)
+    cts = slow.encrypt(msgs, seed=9)
+    assert np.array_equal(fast.encrypt(msgs, seed=9), cts)
+    assert np.array_equal(fast.keyswitch(cts[:4]), slow.keyswitch(cts[:4]))
+    table = (np.arange(16, dtype=np.uint64) * 7 + 3) % 16
+    out = fast.ks_pbs_batch(cts, np.zeros(len(cts), np.uint32), table[None, :])
+    assert np.array_equal(fast.decrypt(out), table[msgs])
+    assert np.std(fast.phase_error(out, table[msgs])) < 4e-5
+    # one CMUX (a~_5 = 1, everything else 0) through both builds: equal up to FFT rounding
+    small = np.zeros(fast.small, dtype=np.uint64)
+    small[5] = np.uint64(1) << np.uint64(52)
+    lut = fast.build_lut(table)
+    err = signed(fast.blind_rotate(small, lut) - slow.blind_rotate(small, lut))
+    assert np.abs(err).max() < 2.0**-20

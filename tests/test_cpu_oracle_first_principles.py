@@ -126,7 +126,9 @@ def test_keyswitch_preserves_phase_within_analytic_noise(keyset):
     sigma = (var_rows + var_round) ** 0.5
     assert np.abs(err).max() < 6 * sigma, (np.abs(err).max(), sigma)
     assert 0.75 * sigma < np.std(err) < 1.25 * sigma, (np.std(err), sigma)
-    assert abs(np.mean(err)) < 4 * sigma / m**0.5
+    # key-dependent offset: the top digit of the balanced decomposition averages +1/2 (never -4), see
+    # tests/test_gpu_first_principles.py
+    assert abs(np.mean(err)) < 4 * 0.5 * p.lwe_std * kN**0.5 + 4 * sigma / m**0.5
 
 
 def test_modswitch_is_rounding_to_2N(keyset):

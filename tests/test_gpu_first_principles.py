@@ -36,7 +36,11 @@ def test_keyswitch_preserves_phase_1e4_samples(engine, keyset):
     sigma = (kN * p.ks_level * 66 / 12.0 * p.lwe_std**2 + (kN / 2.0) * 2.0**-30 / 12.0) ** 0.5
     assert np.abs(err).max() < 6.5 * sigma, (np.abs(err).max(), sigma)
     assert 0.93 * sigma < np.std(err) < 1.07 * sigma, (np.std(err), sigma)
-    assert abs(np.mean(err)) < 4 * sigma / n**0.5
+    # the mean is NOT zero for a fixed key: the most significant digit of the balanced base-8 decomposition
+    # is never -4 (no carry out of the top), so it averages +1/2 and the error carries the key-dependent
+    # offset  1/2 * sum_i e_(i, top level)  ~ N(0, kN / 4 * sigma_lwe^2)  (1.6e-4 rms, 1 % of half a box)
+    bias_sigma = 0.5 * p.lwe_std * kN**0.5
+    assert abs(np.mean(err)) < 4 * bias_sigma + 4 * sigma / n**0.5, (np.mean(err), bias_sigma)
     assert np.array_equal(keyset.decode(keyset.phase_small(small)), msgs)
 
 
