@@ -107,30 +107,135 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
-def string_op_latency(ck, eng):
-    """BASELINE configs[2]: eq / contains / find (+ split) on a 64-char padded encrypted string with
-    an 8-char encrypted pattern; wall-clock per call through the public API (one warm-up call, then
-    the median of 5), host<->device copies of the operand / result blocks included."""
-    from fhe_string_b200.api import ServerKey
-    sk = ServerKey(ck, engine=eng)
-    rng = np.random.default_rng(7)
-    s = "".join(chr(int(c)) for c in rng.integers(33, 127, 40))
-    pat = s[13:21]
-    es, ep = ck.encrypt_str(s, 64), ck.encrypt_str(pat)
-    res = {}
-    for name, call, want in (("eq", lambda: es.eq(sk, es), True), ("contains", lambda: es.contains(sk, ep), True),
-                             ("find", lambda: es.find(sk, ep), 13), ("split", lambda: es.split(sk, ep), s.split(pat))):
-        ts = []
-        call()
-        for _ in range(5):
+def op_suite(eng, rank, world, dist, dev, quick=False):
+    """BASELINE configs[2..4] through the public API at the CURRENT world size, every rank in lock step:
+      config 3: eq / contains / find / split on a 64-char padded string, 8-char pattern (keys l = 255);
+      config 4: to_uppercase / split(" ") / replace(2-char, "c", l=256) on a 256-char padded string
+                (l = 256: 5-block FheUsize);
+      config 5: 1024 independent 64-char comparisons (eq, lt) sliced by rank (fhs_prog_run_many).
+    At N > 1 the ops run through fhs_prog_run_ex sharded: levels above 74 evaluations are split by rank and
+    re-assembled with the library's own ncclAllGather (fhs_comm_allgather) on the context's stream.
+    Per op: `ms` = wall clock per call with HOST operands and a HOST result (H2D + levels + D2H inside, the
+    reference's calling convention), `resident_ms` = operands and result device-resident (what a chain of
+    ops pays), `device_ms` = CUDA events around operand copies + levels of the resident call; medians of 5
+    calls after one warm-up call, max over ranks; results decrypted and compared with Python str."""
+    import torch
+    from fhe_string_b200.api import ClientKey, ServerKey
+
+    def vmax(x):
+        if dist is None:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(call, reps):
+        ts, dv, st = [], [], None
+        r = call()
+        for _ in range(reps):
+            barrier()
             t0 = time.perf_counter()
             r = call()
             ts.append((time.perf_counter() - t0) * 1e3)
-        st = sk.last_stats
-        res[name] = {"ms": float(np.median(ts)), "lut_evals": st["pbs"], "levels": st["levels"],
-                     "correct": r.decrypt(ck) == want}
-    res["config"] = "64-char padded string (40 chars), 8-char pattern, 1 GPU"
-    return res
+            st = dict(sk_cur[0].last_stats)
+            dv.append(st["device_ms"])
+        return r, vmax(float(np.median(ts))), vmax(float(np.median(dv))), st
+
+    sk_cur = [None]
+
+    def run_cfg(l, rows, reps):
+        # same seed => same key material as the uploaded one (keys do not depend on l); every rank makes
+        # the same ciphertexts (counter-based generator), so no operand broadcast is needed
+        ck = ClientKey(l=l, seed=1)
+        res = {}
+        for name, make, call, want in rows:
+            host_sk, res_sk = ServerKey(ck, engine=eng, resident=False), ServerKey(ck, engine=eng, resident=True)
+
+            args_host, args_res = make(ck), make(ck)     # client-side encryption stays outside the timing
+
+            def host_call():
+                sk_cur[0] = host_sk
+                return call(host_sk, *args_host)         # host operands cross PCIe on every call, host result
+
+            def res_call():
+                sk_cur[0] = res_sk
+                return call(res_sk, *args_res)           # uploaded at first use, result stays in HBM
+
+            r1, ms, _, st = timed(host_call, reps)
+            r2, rms, dms, st2 = timed(res_call, reps)
+            ok = (r1.decrypt(ck) == want) and (r2.decrypt(ck) == want)
+            res[name] = {"ms": ms, "resident_ms": rms, "device_ms": dms, "lut_evals": st["pbs"],
+                         "levels": st["levels"], "sharded_levels": st2["sharded_levels"], "correct": bool(ok)}
+        return res
+
+    out = {"n_gpus": world, "unit": "ms per call: median of 5 after a warm-up call, max over ranks",
+           "exchange": ("fhs_comm_allgather: ncclAllGather in place on the context's stream, levels > 74 LUT "
+                        "evaluations split by rank") if world > 1 else "none (1 GPU)"}
+    reps = 3 if quick else 5
+    # ---- config 3 ----
+    rng = np.random.default_rng(7)
+    s = "".join(chr(int(c)) for c in rng.integers(33, 127, 40))
+    pat = s[13:21]
+    mk2 = lambda a, pa, b, pb: (lambda ck: (ck.encrypt_str(a, pa), ck.encrypt_str(b, pb)))
+    out["config3_64char"] = run_cfg(255, [
+        ("eq", mk2(s, 64, s, 64), lambda sk, a, b: a.eq(sk, b), True),
+        ("contains", mk2(s, 64, pat, None), lambda sk, a, b: a.contains(sk, b), True),
+        ("find", mk2(s, 64, pat, None), lambda sk, a, b: a.find(sk, b), 13),
+        ("split", mk2(s, 64, pat, None), lambda sk, a, b: a.split(sk, b), s.split(pat)),
+    ], reps)
+    # ---- config 4 ----
+    rng = np.random.default_rng(11)
+    words = ["".join(chr(int(c)) for c in rng.integers(97, 123, rng.integers(2, 7))) for _ in range(80)]
+    s4 = " ".join(words)[:200]
+    p4 = s4[50:52]
+    out["config4_256char"] = run_cfg(256, [
+        ("to_uppercase", lambda ck: (ck.encrypt_str(s4, 256),), lambda sk, a: a.to_uppercase(sk), s4.upper()),
+        ("split", mk2(s4, 256, " ", None), lambda sk, a, b: a.split(sk, b), s4.split(" ")),
+        ("replace", lambda ck: (ck.encrypt_str(s4, 256), ck.encrypt_str(p4), ck.encrypt_str("c")),
+         lambda sk, a, b, c: a.replace(sk, b, c, 256), s4.replace(p4, "c")),
+    ], 2 if quick else 3)
+    # ---- config 5: independent instances, no exchange ----
+    from fhe_string_b200.program import Program
+    ck = ClientKey(l=255, seed=1)
+    M = 1024
+    per = (M + world - 1) // world
+    lo, hi = min(M, rank * per), min(M, (rank + 1) * per)
+    rng = np.random.default_rng(13)
+    distinct = []
+    for i in range(64):      # 64 distinct pairs (encryption is client-side CPU work), tiled to 1024 instances
+        a = "".join(chr(int(c)) for c in rng.integers(33, 127, 40))
+        b = a if i % 4 == 0 else (a[:20] + "".join(chr(int(c)) for c in rng.integers(33, 127, 20)) if i % 2 else
+                                  "".join(chr(int(c)) for c in rng.integers(33, 127, 40)))
+        distinct.append((a, b, np.concatenate([ck.encrypt_str(a, 64).blocks, ck.encrypt_str(b, 64).blocks])))
+    mine = [distinct[i % 64] for i in range(lo, hi)]
+    inb = np.stack([d[2] for d in mine]) if mine else np.zeros((0, 520, eng.big), np.uint64)
+    pin = torch.empty(inb.shape, dtype=torch.int64, pin_memory=True)     # 8.7 GB / N of operand blocks
+    pin.numpy().view(np.uint64)[...] = inb
+    inb = pin.numpy().view(np.uint64)
+    sweep = {}
+    for op in ("eq", "lt"):
+        prog = Program(op, [65, 65], 0, (), 4, ck.num_blocks_usize)
+        ms_all = []
+        for _ in range(2):          # the first call also grows the device memory pool
+            barrier()
+            t0 = time.perf_counter()
+            res, st = prog.run_many(eng, inb)
+            torch.cuda.synchronize()
+            ms_all.append(vmax((time.perf_counter() - t0) * 1e3))
+        got = [bool(ck.decrypt_blocks(res[m, :1])[0]) for m in range(len(mine))]
+        want = [(a == b) if op == "eq" else (a < b) for a, b, _ in mine]
+        ok = vmax(0.0 if got == want else 1.0) == 0.0
+        dt = min(ms_all)
+        sweep[op] = {"ms": dt, "pairs": M, "lut_evals": prog.pbs_count * M, "levels": prog.depth,
+                     "comparisons_per_s": M / dt * 1e3, "pbs_per_s": prog.pbs_count * M / dt * 1e3, "correct": bool(ok),
+                     "h2d_bytes": int(inb.nbytes) * world}
+    out["config5_1024_comparisons"] = sweep
+    return out
 
 
 def host_threads():
@@ -142,10 +247,20 @@ def host_threads():
         return max(1, os.cpu_count() or 1)
 
 
-def cpu_baseline(ks, tables, threads, target_seconds=12.0):
-    """Oracle (port of the reference's CPU path) on a bounded sample of the same workload."""
+def cpu_arm_keyset():
+    """The CPU arm: the oracle port compiled ON THIS HOST with -march=native (oracle/Makefile `fast`: SoA
+    radix-4 FFT, per-thread scratch).  Falls back to the portable build if the host has no compiler."""
     from oracle import oracle as O
-    threads = threads or max(O.lib().orc_max_threads(), host_threads())
+    try:
+        return O, O.Keyset(seed=1, fast=True), "fast (-O3 -march=native -ffp-contract=fast, radix-4 SoA FFT)"
+    except Exception as e:      # no gcc on the box: the prebuilt portable library still runs
+        return O, O.Keyset(seed=1), f"portable (-march=x86-64-v2; fast build failed: {type(e).__name__})"
+
+
+def cpu_baseline(tables, threads=0, target_seconds=12.0):
+    """Oracle port of the reference's CPU path on a bounded sample of the same workload, all host cores."""
+    O, ks, build = cpu_arm_keyset()
+    threads = threads or max(ks.L.orc_max_threads(), host_threads())
     msgs, cts, lut_id = synth_inputs(ks, 2 * threads, seed=4242)
     t0 = time.perf_counter()
     ks.ks_pbs_batch(cts, lut_id, tables, threads=threads)
@@ -158,39 +273,44 @@ def cpu_baseline(ks, tables, threads, target_seconds=12.0):
     out = ks.ks_pbs_batch(cts, lut_id, tables, threads=threads)
     dt = time.perf_counter() - t0
     ok = bool(np.array_equal(ks.decrypt(out), tables[lut_id, msgs]))
-    return {"value": n / dt, "unit": "PBS/s", "cores": int(threads), "kind": "port",
+    return {"value": n / dt, "unit": "PBS/s", "cores": int(threads), "kind": "port", "per_core": n / dt / threads,
+            "isa": O.host_isa(), "build": build,
+            "note": "port of the tfhe-rs 0.5 algorithm, not tfhe-rs: concrete-fft with AVX-512 is expected to be "
+                    "about 1.5-2x faster per core than this build",
             "sample": f"{n} of the 4096 KS-PBS of one step, OpenMP over ciphertexts, {dt:.1f} s, "
                       f"decrypt-correct={ok}"}
 
 
 def run_reference(args):
     """CPU arm: the oracle port of the reference's tfhe-rs path (the Rust reference cannot be built
-    here: no cargo, tfhe crate not vendored).  Rank 0 only."""
+    here: no cargo, tfhe crate not vendored), compiled on this host with -march=native.  Rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import oracle as O
-    ks = O.Keyset(seed=1)
+    O, ks, build = cpu_arm_keyset()
     tables = bench_tables()
-    threads = max(O.lib().orc_max_threads(), host_threads())   # not torchrun's OMP_NUM_THREADS=1
-    n = 4 * threads                                   # bounded sample of one 4096-block step
+    threads = max(ks.L.orc_max_threads(), host_threads())   # not torchrun's OMP_NUM_THREADS=1
+    n = 8 * threads                                   # bounded sample of one 4096-block step
     msgs, cts, lut_id = synth_inputs(ks, n, seed=7)
     for _ in range(args.warmup):
         ks.ks_pbs_batch(cts[:threads], lut_id[:threads], tables, threads=threads)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ks.ks_pbs_batch(cts, lut_id, tables, threads=threads)
+        out = ks.ks_pbs_batch(cts, lut_id, tables, threads=threads)
     dt = time.perf_counter() - t0
+    ok = bool(np.array_equal(ks.decrypt(out), tables[lut_id, msgs]))
     v = args.steps * n / dt
-    sample = f"{n} KS-PBS per step (bounded sample of the 4096-block batch), {threads} OpenMP threads"
+    sample = (f"{n} KS-PBS per step (bounded sample of the 4096-block batch), {threads} OpenMP threads, "
+              f"decrypt-correct={ok}")
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": "PBS/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64+u64",
         "data": "synthetic",
         "config": {"workload": "ks_pbs_microbench_4096_PARAM_MESSAGE_2_CARRY_2_KS_PBS",
-                   "batch_per_gpu": BATCH, "reference_arm": "CPU port of the tfhe-rs 0.5 KS-PBS (oracle/)"},
-        "cpu_baseline": {"value": v, "unit": "PBS/s", "cores": threads, "kind": "port", "sample": sample},
+                   "batch_per_gpu": BATCH, "reference_arm": "CPU port of the tfhe-rs 0.5 KS-PBS (oracle/), " + build},
+        "cpu_baseline": {"value": v, "unit": "PBS/s", "cores": threads, "kind": "port", "per_core": v / threads,
+                         "isa": O.host_isa(), "build": build, "sample": sample},
         "e2e": {"value": v, "unit": "PBS/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -205,6 +325,7 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-op-latency", action="store_true", help="skip the string-op latency block (ncu runs)")
+    ap.add_argument("--quick-ops", action="store_true", help="fewer repetitions in the string-op block")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -246,6 +367,8 @@ def main():
         ksk, bsk = ck.ksk(), ck.bsk()
     eng = F.Engine(local)
     eng.upload_keys(p, ksk, bsk, ksk_level_order=0)
+    if world > 1:
+        eng.comm_init_from_torch()      # the library's own NCCL communicator (sharded string ops below)
     # a non-default torch stream: its handle is non-NULL, so the library launches on exactly the
     # stream the torch.cuda.Event timers below are recorded on
     stream = torch.cuda.Stream(device=dev)
@@ -343,6 +466,13 @@ def main():
     else:
         ok_all = ok_dev and ok_e2e
 
+    # ---- string ops (configs 3-5) at this world size: every rank takes part ----
+    ops = None
+    if not args.no_op_latency:
+        torch.cuda.set_stream(torch.cuda.default_stream(dev))
+        eng.set_stream(0)               # the context's own stream from here on
+        ops = op_suite(eng, rank, world, dist, dev, quick=args.quick_ops)
+
     if rank == 0:
         total = batch * world
         value = total * args.steps / (ms_total * 1e-3)
@@ -402,13 +532,8 @@ def main():
                     "ms_per_step": e2e_ms / args.steps},
             "clocks": clocks,
         }
-        if world == 1 and not args.no_op_latency:
-            line["op_latency"] = string_op_latency(ck, eng)
-        if world == 1 and not args.no_cpu_baseline:
-            from oracle import oracle as O      # the cpu_baseline leg: the only use of oracle/ here
-            line["cpu_baseline"] = cpu_baseline(O.Keyset(seed=1), tables, 0)
-        else:
-            line["cpu_baseline"] = None
+        line["op_latency"] = ops
+        line["cpu_baseline"] = None if args.no_cpu_baseline else cpu_baseline(tables)   # the only use of oracle/ here
         print(json.dumps(line), flush=True)
     eng.close()
     if dist is not None:
