@@ -182,6 +182,7 @@ def op_suite(eng, rank, world, dist, dev, quick=False):
     s = "".join(chr(int(c)) for c in rng.integers(33, 127, 40))
     pat = s[13:21]
     mk2 = lambda a, pa, b, pb: (lambda ck: (ck.encrypt_str(a, pa), ck.encrypt_str(b, pb)))
+    phase("op suite: config 3")
     out["config3_64char"] = run_cfg(255, [
         ("eq", mk2(s, 64, s, 64), lambda sk, a, b: a.eq(sk, b), True),
         ("contains", mk2(s, 64, pat, None), lambda sk, a, b: a.contains(sk, b), True),
@@ -193,6 +194,7 @@ def op_suite(eng, rank, world, dist, dev, quick=False):
     words = ["".join(chr(int(c)) for c in rng.integers(97, 123, rng.integers(2, 7))) for _ in range(80)]
     s4 = " ".join(words)[:200]
     p4 = s4[50:52]
+    phase("op suite: config 4")
     out["config4_256char"] = run_cfg(256, [
         ("to_uppercase", lambda ck: (ck.encrypt_str(s4, 256),), lambda sk, a: a.to_uppercase(sk), s4.upper()),
         ("split", mk2(s4, 256, " ", None), lambda sk, a, b: a.split(sk, b), s4.split(" ")),
@@ -200,6 +202,7 @@ def op_suite(eng, rank, world, dist, dev, quick=False):
          lambda sk, a, b, c: a.replace(sk, b, c, 256), s4.replace(p4, "c")),
     ], 2 if quick else 3)
     # ---- config 5: independent instances, no exchange ----
+    phase("op suite: config 5")
     from fhe_string_b200.program import Program
     ck = ClientKey(l=255, seed=1)
     M = 1024
@@ -316,6 +319,15 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+_T0 = time.perf_counter()
+
+
+def phase(msg):
+    """Progress line on stderr (rank 0): where a run's wall-clock goes."""
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(f"[bench +{time.perf_counter() - _T0:6.1f}s] {msg}", file=sys.stderr, flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -365,6 +377,7 @@ def main():
         del ksk_t, bsk_t
     else:
         ksk, bsk = ck.ksk(), ck.bsk()
+    phase("keys generated / broadcast")
     eng = F.Engine(local)
     eng.upload_keys(p, ksk, bsk, ksk_level_order=0)
     if world > 1:
@@ -407,6 +420,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    phase("inputs encrypted and uploaded")
     # ---- device-resident timing ----
     for i in range(warm):
         step_dev(i)
@@ -466,12 +480,14 @@ def main():
     else:
         ok_all = ok_dev and ok_e2e
 
+    phase("KS-PBS microbench timed (device + e2e)")
     # ---- string ops (configs 3-5) at this world size: every rank takes part ----
     ops = None
     if not args.no_op_latency:
         torch.cuda.set_stream(torch.cuda.default_stream(dev))
         eng.set_stream(0)               # the context's own stream from here on
         ops = op_suite(eng, rank, world, dist, dev, quick=args.quick_ops)
+        phase("string-op suite done")
 
     if rank == 0:
         total = batch * world
@@ -534,6 +550,7 @@ def main():
         }
         line["op_latency"] = ops
         line["cpu_baseline"] = None if args.no_cpu_baseline else cpu_baseline(tables)   # the only use of oracle/ here
+        phase("cpu baseline done")
         print(json.dumps(line), flush=True)
     eng.close()
     if dist is not None:
