@@ -26,9 +26,9 @@ elif [ "$MODE" = full ]; then
   timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'blind_rotate|keyswitch|ks_digits' -s 9 -c 3 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
   tail -3 gpurun_out/ncu_full.log
 elif [ "$MODE" = wide ]; then
-  timeout 300 python scratch/dev_br.py 148 > gpurun_out/plain_w.log 2>&1 &&
-  timeout 600 ncu --set full --clock-control none --import-source on -k regex:blind_rotate_wide -s 1 -c 1 -f -o gpurun_out/prof_wide python scratch/dev_br.py 148 > gpurun_out/ncu_wide.log 2>&1
+  timeout 300 python tools/dev_br.py 148 > gpurun_out/plain_w.log 2>&1 &&
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:blind_rotate_wide -s 1 -c 1 -f -o gpurun_out/prof_wide python tools/dev_br.py 148 > gpurun_out/ncu_wide.log 2>&1
 elif [ "$MODE" = pair ]; then
-  timeout 300 python scratch/dev_br.py 74 > gpurun_out/plain_p.log 2>&1 &&
-  timeout 600 ncu --set full --clock-control none --import-source on -k regex:blind_rotate_pair -s 1 -c 1 -f -o gpurun_out/prof_pair python scratch/dev_br.py 74 > gpurun_out/ncu_pair.log 2>&1
+  timeout 300 python tools/dev_br.py 74 > gpurun_out/plain_p.log 2>&1 &&
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:blind_rotate_pair -s 1 -c 1 -f -o gpurun_out/prof_pair python tools/dev_br.py 74 > gpurun_out/ncu_pair.log 2>&1
 fi
