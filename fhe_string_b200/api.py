@@ -58,6 +58,12 @@ class ClientKey:
     def msg_mod(self):
         return self.p.message_modulus
 
+    def trivial_blocks(self, values):
+        delta = (1 << 63) // (self.p.message_modulus * self.p.carry_modulus)
+        out = np.zeros((len(values), self.big), dtype=np.uint64)
+        out[:, -1] = np.asarray([int(v) * delta for v in values], dtype=np.uint64)
+        return out
+
     def ksk(self):
         n = ctypes.c_size_t()
         ptr = self.L.fhs_client_ksk(self.h, ctypes.byref(n))
@@ -111,6 +117,9 @@ class ClientKey:
         vals = np.zeros(n.value * self.num_blocks_char, dtype=np.uint64)
         self.L.fhs_string_layout(self.h, s.encode("ascii"), pad, vals.ctypes.data, len(vals), ctypes.byref(n))
         return FheString(self.encrypt_blocks(vals))
+
+    def decrypt_char(self, c):
+        return self._radix(c.blocks, self.num_blocks_char)[0] % 256
 
     def decrypt_str(self, fs):
         chars = self._radix(fs.blocks, self.num_blocks_char)
@@ -214,6 +223,14 @@ class ServerKey:
     def msg_mod(self):
         return self.engine.p.message_modulus
 
+    def trivial_blocks(self, values):
+        """create_trivial_*: mask 0, body = value * Delta (mod.rs:109,266,427 -- not hidden, no noise)."""
+        p = self.engine.p
+        delta = (1 << 63) // (p.message_modulus * p.carry_modulus)
+        out = np.zeros((len(values), self.engine.big), dtype=np.uint64)
+        out[:, -1] = np.asarray([int(v) * delta for v in values], dtype=np.uint64)
+        return out
+
     def _stage(self, parts):
         """Host operand blocks of one call, copied into a page-locked arena that lives with the engine
         (fhs_host_alloc): the H2D transfer is then a direct DMA instead of a staged copy."""
@@ -276,8 +293,51 @@ class BooleanBlock(_Ct):
 
 
 class FheUsize(_Ct):
+    """mod.rs:402-442."""
+
     def decrypt(self, k):
         return k.decrypt_usize(self)
+
+    @staticmethod
+    def new(k, v):
+        """mod.rs:406: encrypt v under the client key k, num_blocks_usize blocks."""
+        return k.encrypt_usize(v)
+
+    @staticmethod
+    def new_trivial(k, v):
+        """mod.rs:426: trivial (unhidden) encryption made by the SERVER key."""
+        nb = k.num_blocks_usize
+        return FheUsize(k.trivial_blocks([(int(v) >> (2 * i)) & 3 for i in range(nb)]))
+
+    @staticmethod
+    def new_from_bool(k, b):
+        """mod.rs:431: b ? 1 : 0 as a usize -- the boolean block followed by trivial zeros, no PBS."""
+        return FheUsize(np.concatenate([b.blocks, k.trivial_blocks([0] * (k.num_blocks_usize - 1))]))
+
+    @staticmethod
+    def max(k):
+        """mod.rs:435: msg_mod ^ num_blocks_usize - 1 (k: ClientKey or ServerKey)."""
+        return k.msg_mod() ** k.num_blocks_usize - 1
+
+
+class FheAsciiChar(_Ct):
+    """mod.rs:31: one char = num_blocks_char radix blocks."""
+
+    def decrypt(self, k):
+        return k.decrypt_char(self)
+
+    def _as_str(self):
+        s = FheString(dev=self._dev) if self._host is None else FheString(self._host)
+        return s
+
+    def is_uppercase(self, k):      # convert.rs:14
+        return k.run("char_is_uppercase", [self._as_str()])
+
+    def is_lowercase(self, k):      # convert.rs:22
+        return k.run("char_is_lowercase", [self._as_str()])
+
+    def is_whitespace(self, k):     # trim.rs:15
+        return k.run("char_is_whitespace", [self._as_str()])
 
 
 class FheOption:
@@ -314,6 +374,15 @@ class FheStringSliceVector:
         """split.rs:32: number of substrings (encrypted)."""
         return self._run(k, "slices_len")
 
+    def truncate(self, k, i):
+        """split.rs:86: drop every substring from index i on (in place, like the reference)."""
+        flags = self._run(k, "slices_truncate", [i])
+        self.v = [(f, start, end) for f, (_, start, end) in zip(flags, self.v)]
+
+    def reverse(self):
+        """split.rs:229: reverse the order of the elements (no server work)."""
+        self.v.reverse()
+
     def get(self, k, i):
         """split.rs:46: the substring at encrypted index i, if existent."""
         return self._run(k, "slices_get", [i])
@@ -334,6 +403,10 @@ def _wrap(desc, out, nbu):
         return BooleanBlock(**t(0, 1))
     if desc == "usize":
         return FheUsize(**t(0, nbu))
+    if desc == "char":
+        return FheAsciiChar(**t(0, len(out)))
+    if desc.startswith("bools:"):
+        return [BooleanBlock(**t(i, i + 1)) for i in range(int(desc.split(":")[1]))]
     if desc.startswith("str:"):
         return FheString(**t(0, len(out)))
     if desc == "opt_usize":
@@ -369,6 +442,40 @@ class FheString(_Ct):
 
     def max_len(self):
         return self.n_chars - 1
+
+    @staticmethod
+    def new(k, s, l=None):
+        """mod.rs:58: FheString::new(client key, s, pad length)."""
+        return k.encrypt_str(s, l)
+
+    @staticmethod
+    def new_trivial(k, s):
+        """mod.rs:96: trivial encryption by the SERVER key (same three checks, no padding)."""
+        if any(ord(c) >= 128 for c in s):
+            raise ValueError("string is not ascii")
+        if "\0" in s:
+            raise ValueError("string contains terminator character")
+        if len(s) > FheString.max_len_with_key(k):
+            raise ValueError("string length exceeds maximum length")
+        vals = [(ord(c) >> (2 * b)) & 3 for c in s + "\0" for b in range(k.num_blocks_char)]
+        return FheString(k.trivial_blocks(vals))
+
+    @staticmethod
+    def max_len_with_key(k):
+        """mod.rs:240."""
+        return FheUsize.max(k)
+
+    def char_at(self, k, i):
+        """mod.rs:217: the char at encrypted index i, 0 when out of bounds."""
+        return k.run("char_at", [self], [i])
+
+    def substr_end(self, k, start, end):
+        """mod.rs:198: self[start..end]."""
+        return k.run("substr_end", [self], [start, end])
+
+    def substr_eq(self, k, i, s):
+        """compare.rs:119: self[i..i+len(s)] == s for a CLEAR offset i."""
+        return k.run("substr_eq", [self, s], (), (int(i),))
 
 
 def _unary(name):

@@ -86,6 +86,16 @@ struct InsertOps : ReplaceOps {
         for (auto &e : sv.v) acc = inc_if(acc, e.is_some);
         return acc;
     }
+    // split.rs:86 truncate(i): entry j stays present iff fewer than i present entries precede it
+    std::vector<Bool> slices_truncate(const FSliceVec &sv, const Rad &i) {
+        Rad n = usize(0);
+        std::vector<Bool> out;
+        for (auto &e : sv.v) {
+            out.push_back(band(Ops::lt(n, i), e.is_some));
+            n = inc_if(n, e.is_some);
+        }
+        return out;
+    }
     // the i-th present piece: one-hot over the entries by (is_some_j && #present before j == i)
     FOptStr slices_get(const FSliceVec &sv, const Rad &i) {
         Rad n = usize(0);

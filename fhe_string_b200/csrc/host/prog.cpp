@@ -66,7 +66,7 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
     // slices_len / slices_get take a FheStringSliceVector exactly as split* returns it: the string,
     // then scalars[0] entries of (is_some, start, end); slices_get is followed by the index usize.
     FSliceVec SV;
-    if (op == "slices_len" || op == "slices_get") {
+    if (op == "slices_len" || op == "slices_get" || op == "slices_truncate") {
         if (n_strings != 1 || n_usize_args != 0 || n_scalars < 1) { g_host_err = "wrong operand count for op " + op; return FHS_ERR_INVALID; }
         SV.s = S[0];
         for (uint64_t e = 0; e < scalars[0]; e++) {
@@ -76,7 +76,7 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
             sl.end = B.in_usize();
             SV.v.push_back(sl);
         }
-        if (op == "slices_get") U.push_back(B.in_usize());
+        if (op == "slices_get" || op == "slices_truncate") U.push_back(B.in_usize());
     }
     B.P.n_inputs = B.P.g.nodes.size();
     auto need = [&](size_t ns, size_t nu) { return n_strings == ns && n_usize_args == nu; };
@@ -110,6 +110,25 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
         if (!need(2, 0)) return bad();
         FOptStr r = op == "strip_prefix" ? o.strip_prefix(S[0], S[1]) : o.strip_suffix(S[0], S[1]);
         B.out_lin(r.is_some); B.out_str(r.val); B.P.desc = "opt_" + str_desc(r.val);
+    }
+    else if (op == "char_is_uppercase" || op == "char_is_lowercase" || op == "char_is_whitespace") {
+        // FheAsciiChar predicates (convert.rs:14,22, trim.rs:15): operand = one char (a "string" of 1 char)
+        if (!need(1, 0) || S[0].ch.size() != 1) return bad();
+        B.out_lin(op == "char_is_whitespace" ? o.is_whitespace(S[0].ch[0]) : o.is_case(S[0].ch[0], op == "char_is_uppercase"));
+        B.P.desc = "bool";
+    }
+    else if (op == "char_at") {          // mod.rs:217
+        if (!need(1, 1)) return bad();
+        B.out_rad(o.char_at(S[0], U[0])); B.P.desc = "char";
+    }
+    else if (op == "substr_end") {       // mod.rs:198  operands: a; usize start, end
+        if (!need(1, 2)) return bad();
+        FStr r = o.substr_end(S[0], U[0], U[1]);
+        B.out_str(r); B.P.desc = str_desc(r);
+    }
+    else if (op == "substr_eq") {        // compare.rs:119  operands: a, b; scalars[0] = clear offset i
+        if (!need(2, 0) || n_scalars < 1) return bad();
+        B.out_lin(o.substr_eq(S[0], (size_t)scalars[0], S[1])); B.P.desc = "bool";
     }
     else if (op == "substr_to" || op == "substr_from") {
         if (!need(1, 1)) return bad();
@@ -149,6 +168,10 @@ int build_op(const std::string &op, Builder &B, const uint32_t *n_chars, size_t 
         B.out_str(r); B.P.desc = str_desc(r);
     }
     else if (op == "slices_len") { B.out_rad(o.slices_len(SV)); B.P.desc = "usize"; }
+    else if (op == "slices_truncate") {   // split.rs:86: the new is_some flags, entry order unchanged
+        for (auto &b : o.slices_truncate(SV, U[0])) B.out_lin(b);
+        B.P.desc = "bools:" + std::to_string(SV.v.size());
+    }
     else if (op == "slices_get") {
         FOptStr r = o.slices_get(SV, U[0]);
         B.out_lin(r.is_some); B.out_str(r.val); B.P.desc = "opt_" + str_desc(r.val);

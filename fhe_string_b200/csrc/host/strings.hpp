@@ -94,6 +94,18 @@ struct StrOps : Ops {
     // compare.rs:113
     Bool eq_ignore_ascii_case(const FStr &a, const FStr &b) { return eq(to_lowercase(a), to_lowercase(b)); }
 
+    // convert.rs:14 / :22  FheAsciiChar::is_uppercase (65..90) / is_lowercase (97..122): the same range test
+    // case_shift uses, as a boolean
+    Bool is_case(const Rad &c, bool upper) {
+        Lin hi = add(c[2], scale(c[3], 4)), lo = add(c[0], scale(c[1], 4));
+        const int h0 = upper ? 4 : 6;
+        Lin hc = g.pbs(hi, [h0](int x) { return x == h0 ? 1 : (x == h0 + 1 ? 2 : 0); }, 0, 2);
+        Lin lc = g.pbs(lo, [](int x) { return (x >= 1 ? 1 : 0) + (x <= 10 ? 2 : 0); }, 1, 3);
+        return g.pbs(add(scale(hc, 4), lc), [](int v) {
+            int h = v >> 2, l = v & 3;
+            return ((h == 1 && (l & 1)) || (h == 2 && (l & 2))) ? 1 : 0; }, 0, 1);
+    }
+
     // trim.rs:15  whitespace = 9..13 or 32
     Bool is_whitespace(const Rad &c) {
         Lin hi = add(c[2], scale(c[3], 4)), lo = add(c[0], scale(c[1], 4));
@@ -219,6 +231,29 @@ struct StrOps : Ops {
         return mask_chars(a, keep);
     }
     FStr substr_from(const FStr &a, const Rad &index) { return shift_left(a, index); }
+    // mod.rs:198 substr_end: a[start..end] = chars i + start < end, shifted left by start
+    FStr substr_end(const FStr &a, const Rad &start, const Rad &end) { return shift_left(substr_to(a, end), start); }
+    // mod.rs:217 char_at: a[i], 0 if out of bounds -- one-hot over the positions (the reference sums
+    // if_then_else_zero(i == j, a[j]) the same way)
+    Rad char_at(const FStr &a, const Rad &i) {
+        std::vector<Rad> terms;
+        for (size_t j = 0; j < a.ch.size(); j++) terms.push_back(select_zero(eq_scalar(i, j), a.ch[j]));
+        return onehot_sum(terms, nb_char);
+    }
+    // compare.rs:119 substr_eq at the CLEAR offset i: for all j: a[i+j] == b[j] || b[j] == 0, a read as 0
+    // past its end (the reference pads with substr_clear and demands an empty overhang: the same predicate)
+    Bool substr_eq(const FStr &a, size_t i, const FStr &b) {
+        std::vector<Bool> bz = zero_mask(b);
+        std::vector<Bool> terms;
+        for (size_t j = 0; j < b.ch.size(); j++) {
+            if (i + j >= a.ch.size()) { terms.push_back(bz[j]); continue; }
+            auto e = eq_bits(a.ch[i + j], b.ch[j]);
+            Lin x = scale(bz[j], 2);
+            for (auto &bit : e) x = add(x, bit);
+            terms.push_back(g.pbs(x, [](int v) { return v >= 2; }, 0, 1));
+        }
+        return all(terms);
+    }
 
     // trim.rs:31
     FStr trim_start(const FStr &a) {

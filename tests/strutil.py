@@ -34,6 +34,10 @@ def decode(desc, out, nbu=4):
         return bool(out[0])
     if desc == "usize":
         return from_blocks(out, nbu)[0]
+    if desc == "char":
+        return from_blocks(out)[0]
+    if desc.startswith("bools:"):
+        return [bool(b) for b in out]
     if desc.startswith("str:"):
         return dec_str(out)
     if desc == "opt_usize":

@@ -133,3 +133,38 @@ def test_bad_lut_id_is_rejected(keys):
         sk.engine._check(sk.engine.L.fhs_ks_pbs_batch(sk.engine.h, cts.ctypes.data, lut.ctypes.data,
                                                        tables.ctypes.data, 2, 3, out.ctypes.data))
     assert "lut_id" in str(e.value)
+
+
+def test_remaining_public_surface(keys):
+    """mod.rs:96,198,217,240,426-437, compare.rs:119, convert.rs:14,22, trim.rs:15, split.rs:86,229 on real
+    ciphertexts: new_trivial / char_at / substr_end / substr_eq / FheAsciiChar predicates / FheUsize
+    constructors / FheStringSliceVector::truncate + reverse."""
+    from fhe_string_b200.api import FheString, FheUsize
+    ck, sk = keys
+    text = "Hello, B200!"
+    s = ck.encrypt_str(text, 16)
+    c = s.char_at(sk, ck.encrypt_usize(7))
+    assert chr(c.decrypt(ck)) == "B"
+    assert c.is_uppercase(sk).decrypt(ck) is True and c.is_lowercase(sk).decrypt(ck) is False
+    assert s.char_at(sk, ck.encrypt_usize(5)).is_whitespace(sk).decrypt(ck) is False
+    assert s.char_at(sk, ck.encrypt_usize(6)).is_whitespace(sk).decrypt(ck) is True
+    assert s.char_at(sk, ck.encrypt_usize(14)).decrypt(ck) == 0                   # out of bounds -> 0
+    assert s.substr_end(sk, ck.encrypt_usize(7), ck.encrypt_usize(11)).decrypt(ck) == "B200"
+    assert s.substr_eq(sk, 7, ck.encrypt_str("B2")).decrypt(ck) is True
+    assert s.substr_eq(sk, 6, ck.encrypt_str("B2")).decrypt(ck) is False
+    # trivial ciphertexts made by the server key are accepted by every op (mod.rs:96, :426)
+    t = FheString.new_trivial(sk, "B200")
+    assert t.decrypt(ck) == "B200"
+    assert s.contains(sk, t).decrypt(ck) is True
+    assert s.find(sk, t).decrypt(ck) == 7
+    assert s.substr_from(sk, FheUsize.new_trivial(sk, 7)).decrypt(ck) == "B200!"
+    assert FheUsize.new_from_bool(sk, s.contains(sk, t)).decrypt(ck) == 1
+    assert FheUsize.max(sk) == 255 == FheUsize.max(ck) == FheString.max_len_with_key(sk)
+    with pytest.raises(ValueError) as e:
+        FheString.new_trivial(sk, "x" * 256)
+    assert str(e.value) == "string length exceeds maximum length"
+    sv = s.split(sk, ck.encrypt_str("l"))
+    sv.truncate(sk, ck.encrypt_usize(2))
+    assert sv.decrypt(ck) == text.split("l")[:2]
+    sv.reverse()
+    assert sv.decrypt(ck) == text.split("l")[:2][::-1]
