@@ -10,32 +10,45 @@ import time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from fhe_string_b200.api import generate_keys  # noqa: E402
 
-WS = "\t\n\x0b\x0c\r "
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+import rust_str as R  # noqa: E402  (Rust std::str semantics: what the reference prints as "Std")
 
 
-def rsplit_rev(s, p, n=-1):
-    return s.rsplit(p, n)[::-1] if p else ([""] + list(s) + [""])[::-1]
+def rust_debug(v):
+    """{:?} of the Rust value the reference prints (main.rs:534-535): "str", true, Some(3), ["a", "b"], ("a", "b")."""
+    if v is None:
+        return "None"
+    if isinstance(v, bool):
+        return "true" if v else "false"
+    if isinstance(v, str):
+        return '"' + v.replace("\\", "\\\\").replace('"', '\\"') + '"'
+    if isinstance(v, (list, tuple)):
+        body = ", ".join(rust_debug(x) for x in v)
+        return "[" + body + "]" if isinstance(v, list) else "(" + body + ")"
+    return str(v)
 
 
-def split_fwd(s, p, n=-1):
-    return s.split(p, n) if p else [""] + list(s) + [""]
+def some(v, wrap):
+    """Option<T> results: the reference prints Some(..) / None."""
+    return v if not wrap or v is None else _Some(v)
 
 
-def split_term(parts):
-    return parts[:-1] if parts and parts[-1] == "" else parts
+class _Some:
+    def __init__(self, v):
+        self.v = v
+
+    def __eq__(self, o):
+        return isinstance(o, _Some) and o.v == self.v
+
+    def __repr__(self):
+        return "Some(" + rust_debug(self.v) + ")"
 
 
-def split_incl(s, p):
-    out, i = [], 0
-    while p:
-        j = s.find(p, i)
-        if j < 0:
-            break
-        out.append(s[i:j + len(p)])
-        i = j + len(p)
-    if i < len(s):
-        out.append(s[i:])
-    return out
+def dur(sec):
+    """Rust Duration {:?}: ns / µs / ms / s with the unit that keeps the integer part non-zero."""
+    for unit, k in (("s", 1.0), ("ms", 1e-3), ("µs", 1e-6), ("ns", 1e-9)):
+        if sec >= k or unit == "ns":
+            return f"{sec / k:.6g}{unit}"
 
 
 def main():
@@ -51,66 +64,82 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     a = ap.parse_args()
 
-    t0 = time.time()
+    print("Generating keys...")
     ck, sk = generate_keys(a.l, a.seed, a.device)
-    print(f"Generated keys ({time.time() - t0:.2f}s); blocks per usize: {ck.num_blocks_usize}")
+    print("Done.")
     s, p, sub, n = a.input, a.pattern, a.substitution, a.n
-    es, ep, esub = ck.encrypt_str(s, a.pad), ck.encrypt_str(p, a.pad), ck.encrypt_str(sub, a.pad)
+    print("Encrypting input...")
+    es = ck.encrypt_str(s, a.pad)
+    print("Done.\nEncrypting pattern...")
+    ep = ck.encrypt_str(p, a.pad)
+    print("Done.\nEncrypting substitution...")
+    esub = ck.encrypt_str(sub, a.pad)
+    print("Done.\nEncrypting n...")
     en = ck.encrypt_usize(n)
-    opt = lambda v: None if v < 0 else v  # noqa: E731
+    print("Done.")
     L = min(a.l, ck.max_len)
+    q = rust_debug
+    # (name as main.rs prints it, std result, fhe call, result is an Option)  -- order of main.rs:91-508
     cases = [
-        ("len", lambda: len(s), lambda: es.len(sk)),
-        ("is_empty", lambda: s == "", lambda: es.is_empty(sk)),
-        ("eq", lambda: s == p, lambda: es.eq(sk, ep)),
-        ("ne", lambda: s != p, lambda: es.ne(sk, ep)),
-        ("le", lambda: s <= p, lambda: es.le(sk, ep)),
-        ("lt", lambda: s < p, lambda: es.lt(sk, ep)),
-        ("ge", lambda: s >= p, lambda: es.ge(sk, ep)),
-        ("gt", lambda: s > p, lambda: es.gt(sk, ep)),
-        ("eq_ignore_ascii_case", lambda: s.lower() == p.lower(), lambda: es.eq_ignore_ascii_case(sk, ep)),
-        ("contains", lambda: p in s, lambda: es.contains(sk, ep)),
-        ("find", lambda: opt(s.find(p)), lambda: es.find(sk, ep)),
-        ("rfind", lambda: opt(s.rfind(p)), lambda: es.rfind(sk, ep)),
-        ("starts_with", lambda: s.startswith(p), lambda: es.starts_with(sk, ep)),
-        ("ends_with", lambda: s.endswith(p), lambda: es.ends_with(sk, ep)),
-        ("to_lowercase", lambda: s.lower(), lambda: es.to_lowercase(sk)),
-        ("to_uppercase", lambda: s.upper(), lambda: es.to_uppercase(sk)),
-        ("add", lambda: (s + p)[:L], lambda: es.add(sk, ep)),
-        ("repeat", lambda: (s * n)[:L], lambda: es.repeat(sk, en, min(L, len(s * n)))),
-        ("trim", lambda: s.strip(WS), lambda: es.trim(sk)),
-        ("trim_start", lambda: s.lstrip(WS), lambda: es.trim_start(sk)),
-        ("trim_end", lambda: s.rstrip(WS), lambda: es.trim_end(sk)),
-        ("strip_prefix", lambda: s[len(p):] if s.startswith(p) else None, lambda: es.strip_prefix(sk, ep)),
-        ("strip_suffix", lambda: s[:len(s) - len(p)] if s.endswith(p) else None, lambda: es.strip_suffix(sk, ep)),
-        ("replace", lambda: s.replace(p, sub)[:L], lambda: es.replace(sk, ep, esub, min(L, len(s.replace(p, sub))))),
-        ("replacen", lambda: s.replace(p, sub, n)[:L], lambda: es.replacen(sk, ep, esub, en, min(L, len(s.replace(p, sub, n))))),
-        ("split", lambda: split_fwd(s, p), lambda: es.split(sk, ep)),
-        ("rsplit", lambda: rsplit_rev(s, p), lambda: es.rsplit(sk, ep)),
-        ("split_once", lambda: tuple(s.split(p, 1)) if p in s else None, lambda: es.split_once(sk, ep)),
-        ("rsplit_once", lambda: tuple(s.rsplit(p, 1)) if p in s else None, lambda: es.rsplit_once(sk, ep)),
-        ("splitn", lambda: [] if n == 0 else split_fwd(s, p, n - 1), lambda: es.splitn(sk, en, ep)),
-        ("rsplitn", lambda: [] if n == 0 else rsplit_rev(s, p, n - 1), lambda: es.rsplitn(sk, en, ep)),
-        ("split_inclusive", lambda: split_incl(s, p), lambda: es.split_inclusive(sk, ep)),
-        ("split_terminator", lambda: split_term(split_fwd(s, p)), lambda: es.split_terminator(sk, ep)),
-        ("rsplit_terminator", lambda: split_term(s.rsplit(p))[::-1] if p else None, lambda: es.rsplit_terminator(sk, ep)),
-        ("split_ascii_whitespace", lambda: s.split(), lambda: es.split_ascii_whitespace(sk)),
+        (f"{q(s)}.len()", lambda: len(s), lambda: es.len(sk), False),
+        (f"{q(s)}.contains({q(p)})", lambda: p in s, lambda: es.contains(sk, ep), False),
+        (f"{q(s)}.starts_with({q(p)})", lambda: s.startswith(p), lambda: es.starts_with(sk, ep), False),
+        (f"{q(s)}.ends_with({q(p)})", lambda: s.endswith(p), lambda: es.ends_with(sk, ep), False),
+        (f"{q(s)}.find({q(p)})", lambda: R.find(s, p), lambda: es.find(sk, ep), True),
+        (f"{q(s)}.rfind({q(p)})", lambda: R.rfind(s, p), lambda: es.rfind(sk, ep), True),
+        (f"{q(s)}.eq({q(p)})", lambda: s == p, lambda: es.eq(sk, ep), False),
+        (f"{q(s)}.le({q(p)})", lambda: s <= p, lambda: es.le(sk, ep), False),
+        (f"{q(s)}.lt({q(p)})", lambda: s < p, lambda: es.lt(sk, ep), False),
+        (f"{q(s)}.ge({q(p)})", lambda: s >= p, lambda: es.ge(sk, ep), False),
+        (f"{q(s)}.gt({q(p)})", lambda: s > p, lambda: es.gt(sk, ep), False),
+        (f"{q(s)}.ne({q(p)})", lambda: s != p, lambda: es.ne(sk, ep), False),
+        (f"{q(s)}.eq_ignore_ascii_case({q(p)})", lambda: s.lower() == p.lower(), lambda: es.eq_ignore_ascii_case(sk, ep), False),
+        (f"{q(s)}.is_empty()", lambda: s == "", lambda: es.is_empty(sk), False),
+        (f"{q(s)}.add({q(p)})", lambda: (s + p)[:L], lambda: es.add(sk, ep), False),
+        (f"{q(s)}.repeat({n})", lambda: (s * n)[:L], lambda: es.repeat(sk, en, min(L, len(s * n))), False),
+        (f"{q(s)}.replace({q(p)}, {q(sub)})", lambda: R.replace(s, p, sub)[:L],
+         lambda: es.replace(sk, ep, esub, min(L, len(R.replace(s, p, sub)))), False),
+        (f"{q(s)}.replacen({q(p)}, {q(sub)}, {n})", lambda: R.replacen(s, p, sub, n)[:L],
+         lambda: es.replacen(sk, ep, esub, en, min(L, len(R.replacen(s, p, sub, n)))), False),
+        (f"{q(s)}.split({q(p)})", lambda: R.split(s, p), lambda: es.split(sk, ep), False),
+        (f"{q(s)}.rsplit({q(p)})", lambda: R.rsplit(s, p), lambda: es.rsplit(sk, ep), False),
+        (f"{q(s)}.split_once({q(p)})", lambda: R.split_once(s, p), lambda: es.split_once(sk, ep), True),
+        (f"{q(s)}.rsplit_once({q(p)})", lambda: R.rsplit_once(s, p), lambda: es.rsplit_once(sk, ep), True),
+        (f"{q(s)}.splitn({n}, {q(p)})", lambda: R.splitn(s, n, p), lambda: es.splitn(sk, en, ep), False),
+        (f"{q(s)}.rsplitn({n}, {q(p)})", lambda: R.rsplitn(s, n, p), lambda: es.rsplitn(sk, en, ep), False),
+        (f"{q(s)}.split_terminator({q(p)})", lambda: R.split_terminator(s, p), lambda: es.split_terminator(sk, ep), False),
+        (f"{q(s)}.rsplit_terminator({q(p)})", lambda: R.rsplit_terminator(s, p), lambda: es.rsplit_terminator(sk, ep), False),
+        (f"{q(s)}.split_inclusive({q(p)})", lambda: R.split_inclusive(s, p), lambda: es.split_inclusive(sk, ep), False),
+        (f"{q(s)}.split_ascii_whitespace()", lambda: R.split_ascii_whitespace(s), lambda: es.split_ascii_whitespace(sk), False),
+        (f"{q(s)}.trim()", lambda: s.strip(R.WS), lambda: es.trim(sk), False),
+        (f"{q(s)}.trim_start()", lambda: s.lstrip(R.WS), lambda: es.trim_start(sk), False),
+        (f"{q(s)}.trim_end()", lambda: s.rstrip(R.WS), lambda: es.trim_end(sk), False),
+        (f"{q(s)}.strip_prefix({q(p)})", lambda: R.strip_prefix(s, p), lambda: es.strip_prefix(sk, ep), True),
+        (f"{q(s)}.strip_suffix({q(p)})", lambda: R.strip_suffix(s, p), lambda: es.strip_suffix(sk, ep), True),
+        (f"{q(s)}.to_lowercase()", lambda: s.lower(), lambda: es.to_lowercase(sk), False),
+        (f"{q(s)}.to_uppercase()", lambda: s.upper(), lambda: es.to_uppercase(sk), False),
     ]
     ok_all, t_all = True, time.time()
-    for name, std, fhe in cases:
+    for name, std, fhe, is_opt in cases:
         if a.filter and a.filter not in name:
             continue
-        if name == "rsplit_terminator" and not p:
-            continue
+        if ".rsplit_terminator(" in name and not p:
+            continue                                  # the reference's empty-pattern rsplit_terminator is unspecified
         t = time.time(); want = std(); d_std = time.time() - t
-        t = time.time(); enc = fhe(); d_fhe = time.time() - t
-        got = enc.decrypt(ck)
+        t = time.time(); got = fhe().decrypt(ck); d_fhe = time.time() - t      # like main.rs: op + decrypt
+        if isinstance(want, tuple) or isinstance(got, tuple):
+            want, got = (tuple(want) if want is not None else None), (tuple(got) if got is not None else None)
+        want, got = some(want, is_opt), some(got, is_opt)
         st = sk.last_stats
         ok = got == want
         ok_all &= ok
-        print(f"{name}\n  Std: {want!r} ({d_std * 1e6:.0f}us)\n  Fhe: {got!r} ({d_fhe * 1e3:.1f}ms, "
-              f"{st['pbs']} LUT evals in {st['levels']} levels)\n  Equal: {'✅' if ok else '❌'}")
-    print(f"Total: {time.time() - t_all:.2f}s  all equal: {ok_all}")
+        print(f"\n{name}")
+        print(f"Std: {rust_debug(want) if not isinstance(want, _Some) else repr(want)} ({dur(d_std)})")
+        print(f"Fhe: {rust_debug(got) if not isinstance(got, _Some) else repr(got)} ({dur(d_fhe)}; "
+              f"{st['pbs']} LUT evals, {st['levels']} levels, {st['device_ms']:.2f} ms on the GPU)")
+        print(f"Equal: {'✅' if ok else '❌'}")
+    print(f"\nDuration (total): {dur(time.time() - t_all)}")
+    print(f"all equal: {ok_all}")
     return 0 if ok_all else 1
 
 
