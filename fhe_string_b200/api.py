@@ -234,11 +234,15 @@ class ServerKey:
     def _stage(self, parts):
         """Host operand blocks of one call, copied into a page-locked arena that lives with the engine
         (fhs_host_alloc): the H2D transfer is then a direct DMA instead of a staged copy."""
-        n = sum(len(x) for x in parts)
-        if self._arena is None or self._arena.shape[0] < n:
+        pinned = [x.flags["C_CONTIGUOUS"] and self.engine.is_pinned(x) for x in parts]   # e.g. earlier results
+        n = sum(len(x) for x, pin in zip(parts, pinned) if not pin)
+        if n and (self._arena is None or self._arena.shape[0] < n):
             self._arena = self.engine.pinned_blocks(max(2 * n, 1024))
         out, o = [], 0
-        for x in parts:
+        for x, pin in zip(parts, pinned):
+            if pin:
+                out.append(x)
+                continue
             self._arena[o:o + len(x)] = x
             out.append(self._arena[o:o + len(x)])
             o += len(x)
@@ -271,7 +275,7 @@ class ServerKey:
             self.last_stats = p.run_ex(eng, ops, out_dev=buf.ptr, rank=rank, world=world, shard_min=self.shard_min)
             out = _Out(dev=buf)
         else:
-            host = np.empty((p.n_outputs, eng.big), dtype=np.uint64)
+            host = eng.pinned_array(p.n_outputs)      # page-locked: direct DMA, no staged copy
             self.last_stats = p.run_ex(eng, ops, out_host=host, rank=rank, world=world, shard_min=self.shard_min)
             out = _Out(host=host)
         return _wrap(p.desc, out, self.num_blocks_usize)

@@ -1,6 +1,7 @@
 """ctypes binding of include/fhs_cuda.h (libfhs_cuda.so).  Host-side plumbing only."""
 import ctypes
 import os
+import weakref
 
 import numpy as np
 
@@ -136,6 +137,9 @@ class Engine:
             for ch in getattr(self, "_pinned", []):
                 self.L.fhs_host_free(self.h, ctypes.c_void_p(ch))
             self._pinned = []
+            for lst in getattr(self, "_pin_free", {}).values():     # result buffers nobody holds any more
+                while lst:
+                    self.L.fhs_host_free(self.h, ctypes.c_void_p(lst.pop()))
             self.L.fhs_ctx_destroy(self.h)    # also frees cached executions and device arrays' allocator
             self.h = None
 
@@ -169,6 +173,28 @@ class Engine:
         self._pinned.append(int(q.value))
         buf = (ctypes.c_uint64 * (max(1, int(n_blocks)) * self.big)).from_address(q.value)
         return np.ctypeslib.as_array(buf).reshape(-1, self.big)
+
+    def pinned_array(self, n_blocks):
+        """A page-locked u64 [n_blocks][big] array for RESULTS: recycled through a size-class free list when
+        the last numpy view of it is garbage-collected (host-array mode returns these, so a result can be
+        passed back as an operand, or read by the client, without another staging copy)."""
+        if not hasattr(self, "_pin_free"):
+            self._pin_free = {}
+        n = max(1, int(n_blocks))
+        cap = 1 << max(4, (n - 1).bit_length())
+        lst = self._pin_free.setdefault(cap, [])
+        if lst:
+            ptr = lst.pop()
+        else:
+            q = ctypes.c_void_p()
+            self._check(self.L.fhs_host_alloc(self.h, cap * self.big * 8, ctypes.byref(q)))
+            ptr = int(q.value)
+        buf = (ctypes.c_uint64 * (cap * self.big)).from_address(ptr)
+        weakref.finalize(buf, lst.append, ptr)       # back to the free list when every view is gone
+        return np.ctypeslib.as_array(buf).reshape(cap, self.big)[:n_blocks]
+
+    def is_pinned(self, arr):
+        return bool(self.L.fhs_host_is_pinned(ctypes.c_void_p(arr.ctypes.data)))
 
     def cache_stats(self):
         n, b = ctypes.c_size_t(), ctypes.c_size_t()
