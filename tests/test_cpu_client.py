@@ -64,3 +64,25 @@ def test_string_layout_errors(small_params):
             k.encrypt_str(s, l)
         assert str(e.value) == msg                                    # mod.rs:59-71
     assert k.encrypt_str("abc", 5).decrypt(k) == "abc"
+
+
+def test_tfhe_wire_layout_round_trip(small_params):
+    """fhe_string_b200/tfhe_wire.py = the bincode field order INTEGRATION.md expects for the reference's serde
+    types (recalled, unverified against tfhe-rs): self-consistent, size per block as documented, strict about
+    trailing bytes so that a real file falsifies it in one call."""
+    from fhe_string_b200 import tfhe_wire as W
+    k = ClientKey(l=15, seed=5, params=small_params)
+    s = k.encrypt_str("abc", 4)
+    raw = W.dump_fhe_string(s.blocks)
+    lwe = small_params.poly_size + 1
+    assert len(raw) == 8 + 5 * (8 + 4 * (8 + 8 * lwe + 60))            # 60 = 24 (modulus, scalar bits) + 4 x 8 + 4 (pbs_order)
+    back = W.parse_fhe_string(raw)
+    assert np.array_equal(back, s.blocks)
+    from fhe_string_b200.api import FheString
+    assert FheString(back).decrypt(k) == "abc"
+    with pytest.raises(W.WireError):
+        W.parse_fhe_string(raw + b"\0")
+    with pytest.raises(W.WireError):
+        W.parse_fhe_string(raw[:-3])
+    # the documented size for the real parameter set: 16 460 bytes per block
+    assert 8 + 8 * 2049 + W.BLOCK_META.size == 16460
