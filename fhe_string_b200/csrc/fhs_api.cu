@@ -338,6 +338,11 @@ int fhs_upload_keys_fourier(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk
     return upload_keys_impl(h, p, ksk, ksk_level_order, bsk_fourier, fourier_convention);
 }
 
+int fhs_upload_keys_fmt(fhs_ctx *h, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
+                        const void *bsk, int bsk_format) {
+    return upload_keys_impl(h, p, ksk, ksk_level_order, bsk, bsk_format);
+}
+
 // host-pointer entry points: every lut_id must name a row of lut_tables (device-pointer calls cannot be
 // checked without a synchronisation; there the kernels clamp the id)
 static int check_lut_ids(const uint32_t *lut_id, size_t batch, size_t n_luts) {

@@ -240,6 +240,12 @@ int fhs_level(fhs_pool *hp, size_t B, const uint32_t *term_off, const uint32_t *
     return fhs_ks_pbs_batch_dev(reinterpret_cast<fhs_ctx *>(c), p->d_stage, p->d_lut, p->d_tables, n_luts, B, dst);
 }
 
+int fhs_level_d(fhs_pool *hp, const fhs_level_desc *d) {
+    if (!d) return FHS_ERR_INVALID;
+    return fhs_level(hp, d->B, d->term_off, d->term_idx, d->term_coef, d->const_body, d->lut_id, d->lut_tables,
+                     d->n_luts, d->out_slot);
+}
+
 // Upload on a side stream: returns once the host buffer has been consumed (pageable memory is staged
 // by the runtime), the DMA itself overlaps with kernels already queued on the context's stream.
 // fhs_pool_wait_writes makes the context's stream wait for it.  The caller guarantees that no

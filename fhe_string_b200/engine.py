@@ -38,7 +38,7 @@ EXPORTS = [
     "fhs_measure_fp64_tflops",
     "fhs_pool_enqueue_write", "fhs_pool_enqueue_read", "fhs_pool_copy_in", "fhs_pool_copy_out",
     "fhs_dev_alloc", "fhs_dev_free", "fhs_dev_write", "fhs_dev_read", "fhs_host_alloc", "fhs_host_free",
-    "fhs_host_is_pinned", "fhs_ctx_cache_get", "fhs_ctx_cache_put", "fhs_cache_drop_owner",
+    "fhs_upload_keys_fmt", "fhs_level_d", "fhs_host_is_pinned", "fhs_ctx_cache_get", "fhs_ctx_cache_put", "fhs_cache_drop_owner",
     "fhs_ctx_cache_stats", "fhs_ctx_cache_limit", "fhs_ctx_timer_start", "fhs_ctx_timer_stop", "fhs_ctx_timer_ms",
 ]
 

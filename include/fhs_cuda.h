@@ -95,6 +95,15 @@ int fhs_upload_keys(fhs_ctx *ctx, const fhs_params *p, const uint64_t *ksk, int 
 int fhs_upload_keys_fourier(fhs_ctx *ctx, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
                             const double *bsk_fourier, int fourier_convention);
 
+/* The two calls above behind ONE entry point with a format flag, as SURVEY.md 8(b) words the boundary:
+ * bsk_format FHS_BSK_STANDARD = u64 [n][lvl][k+1][k+1][N] coefficient-domain rows, FHS_BSK_FOURIER_POS /
+ * _NEG = c64 natural-order spectra with that exponent sign. */
+#define FHS_BSK_STANDARD (-1)
+#define FHS_BSK_FOURIER_POS FHS_FOURIER_NATURAL_POS
+#define FHS_BSK_FOURIER_NEG FHS_FOURIER_NATURAL_NEG
+int fhs_upload_keys_fmt(fhs_ctx *ctx, const fhs_params *p, const uint64_t *ksk, int ksk_level_order,
+                        const void *bsk, int bsk_format);
+
 /* One level of independent LUT evaluations, host buffers (copies inside the call).
  * Replaces B calls of shortint apply_lookup_table (tfhe keyswitch_programmable_bootstrap_assign),
  * reached from e.g. src/ciphertext/compare.rs:32,74,130-132, src/ciphertext/logic.rs:13-65.
@@ -154,6 +163,21 @@ int fhs_pool_read(fhs_pool *pool, size_t slot, size_t n, uint64_t *host_blocks);
 int fhs_level(fhs_pool *pool, size_t B, const uint32_t *term_off, const uint32_t *term_idx,
               const int32_t *term_coef, const uint64_t *const_body, const uint32_t *lut_id,
               const uint64_t *lut_tables, size_t n_luts, size_t out_slot);
+
+/* fhs_level with its arguments as one descriptor (the form SURVEY.md 8(b) gives):
+ *   B evaluations; gather idx / coef as CSR (term_off[B+1]); const_body[B] scaled by Delta; lut_id[B] or
+ *   NULL for a purely linear level; results in pool slots [out_slot, out_slot + B). */
+typedef struct {
+    size_t B;
+    const uint32_t *term_off, *term_idx;
+    const int32_t *term_coef;
+    const uint64_t *const_body;
+    const uint32_t *lut_id;
+    const uint64_t *lut_tables;
+    size_t n_luts;
+    size_t out_slot;
+} fhs_level_desc;
+int fhs_level_d(fhs_pool *pool, const fhs_level_desc *level);
 
 /* Side-stream upload into a pool (overlaps with levels already queued on the context's stream) and
  * the matching wait of the context's stream.  Used by fhs_prog_run_many to hide the H2D of the next
