@@ -486,7 +486,10 @@ def main():
     if not args.no_op_latency:
         torch.cuda.set_stream(torch.cuda.default_stream(dev))
         eng.set_stream(0)               # the context's own stream from here on
-        ops = op_suite(eng, rank, world, dist, dev, quick=args.quick_ops)
+        try:
+            ops = op_suite(eng, rank, world, dist, dev, quick=args.quick_ops)
+        except Exception as e:       # the headline line must survive a failure of the secondary block
+            ops = {"error": f"{type(e).__name__}: {e}"}
         phase("string-op suite done")
 
     if rank == 0:
