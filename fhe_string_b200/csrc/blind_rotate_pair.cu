@@ -304,7 +304,9 @@ blind_rotate_pair_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
             p_twiddle8<false, false>(xr, xi, tw);
 #pragma unroll
             for (int k0 = 0; k0 < 8; k0++) E2[(k1p * 8 + k0) * kPE2Stride + t0] = make_double2(xr[k0], xi[k0]);
-            pbar_sync(kPBarAll, 128);
+            // rows 16 v .. 16 v + 15 of E2 are written and read by warp v alone (k1p = k1q = t >> 4): a
+            // warp-level sync replaces the 128-thread barrier of round 1
+            __syncwarp();
             tmem_ld32(ttw3, tw);
 #pragma unroll
             for (int u = 0; u < 8; u++) {
@@ -384,7 +386,7 @@ blind_rotate_pair_kernel(const uint64_t *__restrict__ lwe_small, const uint32_t 
             fft8_neg_lo(xr, xi);
 #pragma unroll
             for (int u = 0; u < 8; u++) E2[(k1q * 8 + kq) * kPE2Stride + 2 * u + s] = make_double2(xr[u], xi[u]);
-            pbar_sync(kPBarAll, 128);
+            __syncwarp();                           // warp-private rows, as in the forward exchange
             tmem_ld32(ttw2, tw);
 #pragma unroll
             for (int k0 = 0; k0 < 8; k0++) {
