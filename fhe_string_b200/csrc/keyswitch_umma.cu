@@ -13,6 +13,8 @@
 //     "empty" barrier, warps 2-5 read the 256 s32 accumulator columns back with tcgen05.ld and
 //     recombine the 8 limbs of every output coefficient.
 // Integer arithmetic only: bit-exact against the oracle (tests/test_gpu_parity.py).
+#include <mutex>
+
 #include "fhs_internal.cuh"
 #include "tmem.cuh"
 
@@ -256,3 +258,84 @@ int launch_keyswitch_umma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *
 }
 
 }  // namespace fhs
+
+// ---- allocation-free KS-PBS (include/fhs_cuda.h fhs_ks_pbs_batch_dev_noalloc) ----------------------------
+// For callers that may not allocate (a stream under graph capture, a serving loop, a harness that forbids
+// cudaMalloc): the two scratch arrays of the path -- the digit tiles of the tensor-core keyswitch and the
+// keyswitched small LWE ciphertexts handed to the blind rotation -- live in file-scope device arrays sized
+// for FHS_NOALLOC_MAX_BATCH ciphertexts instead of the context's grow-on-demand buffers.  Every GPU that
+// loads the library holds them (6.3 MB) until exit.  Both arrays are overwritten in full before they are
+// read (ks_digits_kernel zero-fills the rows past the batch; the keyswitch writes every word of every row
+// below it), so nothing carries over from the previous call; but all calls on a GPU share them: calls that
+// overlap on the device (two streams, two contexts) race.
+namespace fhs {
+namespace {
+constexpr size_t kNoAllocMTiles = (FHS_NOALLOC_MAX_BATCH + kUM - 1) / kUM;
+constexpr size_t kNoAllocKb = 2048 / kUK;                       // K-blocks of the big LWE mask (k N = 2048)
+constexpr size_t kNoAllocSmallW = 768;                          // >= n + 1 (keyswitch.cu: n + 1 <= 768)
+static __device__ __align__(256) uint8_t g_noalloc_digits[kNoAllocMTiles * kNoAllocKb * kAStage];
+static __device__ __align__(256) uint64_t g_noalloc_small[(size_t)FHS_NOALLOC_MAX_BATCH * kNoAllocSmallW];
+
+// The arrays' names are host-side stand-ins here: the device addresses come from cudaGetSymbolAddress,
+// once per device, with that device current.
+constexpr int kNoAllocMaxDev = 64;
+struct NoAllocAddr { uint8_t *digits; uint64_t *small; bool ok; };
+NoAllocAddr g_noalloc_addr[kNoAllocMaxDev];
+std::mutex g_noalloc_mu;
+
+int noalloc_addresses(int device, uint8_t **digits, uint64_t **small) {
+    if (device < 0 || device >= kNoAllocMaxDev) { set_error("device %d out of range", device); return FHS_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    NoAllocAddr &a = g_noalloc_addr[device];
+    if (!a.ok) {
+        FHS_CUDA(cudaSetDevice(device));
+        FHS_CUDA(cudaGetSymbolAddress(reinterpret_cast<void **>(&a.digits), g_noalloc_digits));
+        FHS_CUDA(cudaGetSymbolAddress(reinterpret_cast<void **>(&a.small), g_noalloc_small));
+        a.ok = true;
+    }
+    *digits = a.digits;
+    *small = a.small;
+    return FHS_OK;
+}
+}  // namespace
+}  // namespace fhs
+
+extern "C" int fhs_ks_pbs_batch_dev_noalloc(fhs_ctx *h, const uint64_t *d_in, const uint32_t *d_lut_id,
+                                            const uint64_t *d_tables, size_t n_luts, size_t batch, uint64_t *d_out) {
+    using namespace fhs;
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c) return FHS_ERR_INVALID;
+    if (!c->has_keys) { set_error("keys not uploaded"); return FHS_ERR_NO_KEYS; }
+    if (batch == 0) return FHS_OK;
+    if (!d_in || !d_lut_id || !d_tables || !d_out || n_luts == 0) { set_error("null buffer or empty LUT table"); return FHS_ERR_INVALID; }
+    if (batch > (size_t)FHS_NOALLOC_MAX_BATCH) {
+        set_error("fhs_ks_pbs_batch_dev_noalloc: batch %zu exceeds the static scratch (FHS_NOALLOC_MAX_BATCH = %d); "
+                  "split the batch or use fhs_ks_pbs_batch_dev", batch, FHS_NOALLOC_MAX_BATCH);
+        return FHS_ERR_INVALID;
+    }
+    if (c->big != kNoAllocKb * kUK || (size_t)c->n + 1 > kNoAllocSmallW || c->p.ks_level != kLv || c->p.ks_base_log != kBl) {
+        set_error("fhs_ks_pbs_batch_dev_noalloc: static scratch is sized for k N = 2048, n + 1 <= 768, KS 2^3 x 5");
+        return FHS_ERR_INVALID;
+    }
+    FHS_CUDA(cudaSetDevice(c->device));
+    uint8_t *digits = nullptr;
+    uint64_t *small = nullptr;
+    int rc = noalloc_addresses(c->device, &digits, &small);
+    if (rc != FHS_OK) return rc;
+    const int smem_bytes = kStages * (kAStage + kBStage);
+    if (!c->attr_ksu) {
+        FHS_CUDA(cudaFuncSetAttribute(keyswitch_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        c->attr_ksu = true;
+    }
+    const int n_kb = (int)kNoAllocKb;
+    const unsigned m_tiles = (unsigned)((batch + kUM - 1) / kUM);
+    ks_digits_kernel<<<dim3(n_kb, m_tiles), 256, 0, c->stream>>>(d_in, digits, (unsigned int)batch, (int)c->big, n_kb);
+    c->launches++;
+    FHS_CUDA(cudaGetLastError());
+    const int n_tiles = (int)(((size_t)(c->n + 1) * 8 + kUN - 1) / kUN);
+    keyswitch_umma_kernel<<<dim3(n_tiles, m_tiles), kThreadsU, smem_bytes, c->stream>>>(
+        digits, c->d_ksk_u, d_in, small, (unsigned int)batch, (int)c->n, (int)c->big, n_kb);
+    c->launches++;
+    FHS_CUDA(cudaGetLastError());
+    return launch_blind_rotate(c, small, d_lut_id, d_tables, n_luts, batch, d_out);
+}

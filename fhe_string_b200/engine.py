@@ -33,7 +33,7 @@ EXPORTS = [
     "fhs_ctx_set_stream", "fhs_ctx_synchronize", "fhs_upload_keys", "fhs_upload_keys_fourier", "fhs_ks_pbs_batch",
     "fhs_comm_unique_id", "fhs_comm_init", "fhs_comm_info", "fhs_comm_destroy", "fhs_comm_allgather",
     "fhs_comm_broadcast_host",
-    "fhs_ks_pbs_batch_dev", "fhs_keyswitch_batch", "fhs_keyswitch_batch_dev", "fhs_build_lut",
+    "fhs_ks_pbs_batch_dev", "fhs_ks_pbs_batch_dev_noalloc", "fhs_keyswitch_batch", "fhs_keyswitch_batch_dev", "fhs_build_lut",
     "fhs_pbs_batch", "fhs_pbs_batch_dev", "fhs_last_kernel_ms", "fhs_launch_count",
     "fhs_measure_fp64_tflops",
     "fhs_pool_enqueue_write", "fhs_pool_enqueue_read", "fhs_pool_copy_in", "fhs_pool_copy_out",
@@ -80,6 +80,7 @@ def load_library():
     L.fhs_comm_broadcast_host.argtypes = [vp, vp, ctypes.c_size_t, ctypes.c_int]
     L.fhs_ks_pbs_batch.argtypes = [vp, vp, vp, vp, sz, sz, vp]
     L.fhs_ks_pbs_batch_dev.argtypes = [vp, vp, vp, vp, sz, sz, vp]
+    L.fhs_ks_pbs_batch_dev_noalloc.argtypes = [vp, vp, vp, vp, sz, sz, vp]
     L.fhs_keyswitch_batch.argtypes = [vp, vp, sz, vp]
     L.fhs_keyswitch_batch_dev.argtypes = [vp, vp, sz, vp]
     L.fhs_build_lut.argtypes = [vp, vp, vp]
@@ -329,6 +330,11 @@ class Engine:
     # ---- device-pointer entry points (ints from torch .data_ptr()) ----
     def ks_pbs_dev(self, d_in, d_lut_id, d_tables, n_luts, batch, d_out):
         self._check(self.L.fhs_ks_pbs_batch_dev(self.h, d_in, d_lut_id, d_tables, n_luts, batch, d_out))
+
+    def ks_pbs_dev_noalloc(self, d_in, d_lut_id, d_tables, n_luts, batch, d_out):
+        """fhs_ks_pbs_batch_dev_noalloc: same results, scratch in the library's static device arrays, at most
+        NOALLOC_MAX_BATCH ciphertexts per call (include/fhs_cuda.h)."""
+        self._check(self.L.fhs_ks_pbs_batch_dev_noalloc(self.h, d_in, d_lut_id, d_tables, n_luts, batch, d_out))
 
     def keyswitch_dev(self, d_in, batch, d_out):
         self._check(self.L.fhs_keyswitch_batch_dev(self.h, d_in, batch, d_out))

@@ -117,6 +117,20 @@ int fhs_ks_pbs_batch(fhs_ctx *ctx, const uint64_t *lwe_in, const uint32_t *lut_i
 int fhs_ks_pbs_batch_dev(fhs_ctx *ctx, const uint64_t *d_lwe_in, const uint32_t *d_lut_id,
                          const uint64_t *d_lut_tables, size_t n_luts, size_t batch,
                          uint64_t *d_lwe_out);
+/* Same as fhs_ks_pbs_batch_dev for callers that may not allocate (a stream under CUDA graph capture, a
+ * tight serving loop, a harness that forbids cudaMalloc).  No counterpart in the reference.
+ * The path's scratch (keyswitch digit tiles + the keyswitched small LWE
+ * ciphertexts) is a pair of file-scope device arrays in the library, 6.3 MB per GPU held until process exit,
+ * instead of the context's grow-on-demand buffers; the call makes no cudaMalloc / cudaFree and calls no
+ * allocating routine.  batch > FHS_NOALLOC_MAX_BATCH -> FHS_ERR_INVALID (fhs_last_error names the limit);
+ * parameter sets other than k N = 2048, n + 1 <= 768, KS 2^3 x 5 likewise.  Results are bit-identical to
+ * fhs_ks_pbs_batch_dev.  All calls on one GPU share the arrays: each call overwrites what it reads, so
+ * calls in sequence on one stream are independent, but calls that overlap on the GPU (two streams, two
+ * contexts on the same device) race.  Asynchronous on the context's stream, like fhs_ks_pbs_batch_dev. */
+#define FHS_NOALLOC_MAX_BATCH 384
+int fhs_ks_pbs_batch_dev_noalloc(fhs_ctx *ctx, const uint64_t *d_lwe_in, const uint32_t *d_lut_id,
+                                 const uint64_t *d_lut_tables, size_t n_luts, size_t batch,
+                                 uint64_t *d_lwe_out);
 
 /* Verification entry points for the bit-exact tiers. */
 /* tfhe keyswitch_lwe_ciphertext on a batch: [B][k*N+1] -> [B][n+1]; host buffers. */
