@@ -114,7 +114,8 @@ def op_suite(eng, rank, world, dist, dev, quick=False):
                 (l = 256: 5-block FheUsize);
       config 5: 1024 independent 64-char comparisons (eq, lt) sliced by rank (fhs_prog_run_many).
     At N > 1 the ops run through fhs_prog_run_ex sharded: levels above 74 evaluations are split by rank and
-    re-assembled with the library's own ncclAllGather (fhs_comm_allgather) on the context's stream.
+    re-assembled by the library's own peer-window kernel (fhs_pool_peer_allgather: stores into the peers' pools
+    over NVLink), or by ncclAllGather (fhs_comm_allgather) where peer windows are unavailable.
     Per op: `ms` = wall clock per call with HOST operands and a HOST result (H2D + levels + D2H inside, the
     reference's calling convention), `resident_ms` = operands and result device-resident (what a chain of
     ops pays), `device_ms` = CUDA events around operand copies + levels of the resident call; medians of 5
@@ -238,6 +239,13 @@ def op_suite(eng, rank, world, dist, dev, quick=False):
                      "comparisons_per_s": M / dt * 1e3, "pbs_per_s": prog.pbs_count * M / dt * 1e3, "correct": bool(ok),
                      "h2d_bytes": int(inb.nbytes) * world}
     out["config5_1024_comparisons"] = sweep
+    if world > 1:
+        pushes = eng.peer_pushes()
+        out["exchange"] = (("fhs_pool_peer_allgather: one kernel of the library stores a rank's result blocks into every "
+                            "peer's pool over NVLink peer memory (CUDA IPC) and waits on sequence numbers; "
+                            f"{pushes} such exchanges in this suite") if pushes else
+                           "fhs_comm_allgather: ncclAllGather in place on the context's stream (peer windows unavailable or FHS_COMM_P2P=0)") \
+            + "; levels > 74 LUT evaluations split by rank"
     return out
 
 

@@ -71,8 +71,8 @@ def main():
             torch.cuda.synchronize()
             dt = (time.perf_counter() - t0) * 1e3
         if rank == 0:
-            from fhe_string_b200.api import _wrap
-            got = _wrap(prog.desc, out, nbu).decrypt(ck)
+            from fhe_string_b200.api import _Out, _wrap
+            got = _wrap(prog.desc, _Out(host=out), nbu).decrypt(ck)
             want = {"to_uppercase": s.upper(), "contains": True, "find": 100}[op]
             results[op] = {"ms": dt, "lut_evals": prog.pbs_count, "levels": prog.depth, "correct": got == want}
     if rank == 0:

@@ -104,6 +104,9 @@ static void read_knobs(Ctx *c) {
     c->knobs.ks_mma_min = (int)env_int("FHS_KS_MMA_MIN", 1);
     c->knobs.bsk_f64 = env_int("FHS_BSK_XF", 1) == 0;
     c->knobs.ks_baseline_keys = c->knobs.ks_variant != 3 || c->knobs.ks_umma_min > 1;
+    c->knobs.peer_p2p = (int)env_int("FHS_COMM_P2P", 1);
+    c->knobs.peer_timeout_ms = env_int("FHS_PEER_TIMEOUT_MS", 30000);
+    if (c->knobs.peer_timeout_ms < 1) c->knobs.peer_timeout_ms = 1;
 }
 
 int fhs_ctx_create(int device, fhs_ctx **out) {

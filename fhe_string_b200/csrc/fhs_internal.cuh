@@ -45,6 +45,8 @@ struct Ctx {
         int ks_mma_min = 1;        // FHS_KS_MMA_MIN
         int bsk_f64 = 0;           // FHS_BSK_XF=0: plain f64 key transform instead of double-double
         int ks_baseline_keys = 0;  // key forms of the baseline keyswitch kernels are resident (variant != 3)
+        int peer_p2p = 1;          // FHS_COMM_P2P=0: sharded levels exchange with ncclAllGather instead of the peer-window kernel
+        long peer_timeout_ms = 30000;   // FHS_PEER_TIMEOUT_MS: a wait for another rank gives up after this long
     } knobs;
     double2 *d_twiddle = nullptr;  // [32][33] inter-pass twiddles T[k2][n1]
     // scratch
@@ -60,6 +62,7 @@ struct Ctx {
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     bool ev_valid[2] = {false, false};
     uint64_t launches = 0;
+    unsigned long long peer_pushes = 0;   // level.cu: peer-window all-gathers launched
     int sm_count = 0;
     // cudaFuncSetAttribute is per device: done once per context, not once per process
     bool attr_br = false, attr_brw = false, attr_ks = false, attr_ksu = false;

@@ -335,7 +335,7 @@ struct Exec {
 
 void exec_dtor(void *e) { delete static_cast<Exec *>(e); }
 
-int build_exec(const fhs_prog *p, fhs_ctx *ctx, int rank, int world, size_t shard_min, Exec **out) {
+int build_exec(const fhs_prog *p, fhs_ctx *ctx, int rank, int world, size_t shard_min, bool own_comm, Exec **out) {
     const Graph &g = p->g;
     fhs_params prm;
     int rc = fhs_ctx_get_params(ctx, &prm);
@@ -408,7 +408,11 @@ int build_exec(const fhs_prog *p, fhs_ctx *ctx, int rank, int world, size_t shar
     E->slots = next ? next : 1;
     std::vector<uint64_t> tables(g.luts.size() * 16);
     for (size_t i = 0; i < g.luts.size(); i++) memcpy(&tables[16 * i], g.luts[i].data(), 16 * sizeof(uint64_t));
-    if ((rc = fhs_pool_create(ctx, E->slots, &E->pool)) != FHS_OK) return rc;
+    // a program with split levels gets a pool the other ranks can store into (peer window); the call is
+    // collective, and every rank builds the execution state of an operation at the same point
+    if (world > 1 && E->n_sharded && own_comm) rc = fhs_pool_create_shared(ctx, E->slots, &E->pool);
+    else rc = fhs_pool_create(ctx, E->slots, &E->pool);
+    if (rc != FHS_OK) return rc;
     if ((rc = fhs_pool_load_program(E->pool, cst.size(), idx.size(), off.data(), idx.data(), coef.data(), cst.data(),
                                     lut.data(), tables.data(), g.luts.size(), max_rows)) != FHS_OK) return rc;
     *out = E.release();
@@ -468,13 +472,14 @@ extern "C" int fhs_prog_run_ex(const fhs_prog *p, fhs_ctx *ctx, const fhs_operan
     Exec *E = static_cast<Exec *>(obj);
     const bool cached = E != nullptr;
     if (!E) {
-        if ((rc = build_exec(p, ctx, rank, world, shard_min, &E)) != FHS_OK) { delete E; return rc; }
+        if ((rc = build_exec(p, ctx, rank, world, shard_min, allgather == nullptr, &E)) != FHS_OK) { delete E; return rc; }
         if ((rc = fhs_ctx_cache_put(ctx, key, E, exec_dtor, E->slots * E->width * sizeof(uint64_t))) != FHS_OK) { delete E; return rc; }
     }
     const double plan_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
     const size_t width = E->width, n_out = E->n_out;
     const uint64_t launches0 = fhs_launch_count(ctx);
     fhs_pool *pool = E->pool;
+    const bool peer_window = world > 1 && fhs_pool_is_shared(pool);
     bool timed = fhs_ctx_timer_start(ctx) == FHS_OK;
     do {
         // ---- operands: device arrays are copied on the device; host arrays go by DMA straight from
@@ -500,7 +505,10 @@ extern "C" int fhs_prog_run_ex(const fhs_prog *p, fhs_ctx *ctx, const fhs_operan
             if (G.per) {  // exchange result blocks: rank q owns [out_base + q*per, out_base + (q+1)*per)
                 uint64_t *base = fhs_pool_device_ptr(pool) + G.out_base * width;
                 const size_t bytes = G.per * width * sizeof(uint64_t);
-                if (!allgather) {
+                if (!allgather && peer_window) {
+                    // one kernel of our own: stores into the peers' pools over NVLink + sequence numbers
+                    if ((rc = fhs_pool_peer_allgather(pool, G.out_base, G.per, G.hi - G.lo)) != FHS_OK) break;
+                } else if (!allgather) {
                     // ncclAllGather in place, on the stream the level's kernels run on: no host sync
                     if ((rc = fhs_comm_allgather(ctx, base, bytes)) != FHS_OK) break;
                 } else {
@@ -514,6 +522,8 @@ extern "C" int fhs_prog_run_ex(const fhs_prog *p, fhs_ctx *ctx, const fhs_operan
             if ((rc = fhs_level_run(pool, E->OG.row0, n_out, 0, E->OG.out_base)) != FHS_OK) break;
             if (out_dev && (rc = fhs_pool_copy_out(pool, E->OG.out_base, n_out, out_dev)) != FHS_OK) break;
         }
+        // nothing below reads blocks another rank wrote: the peers may start overwriting them
+        if (peer_window && !allgather && (rc = fhs_pool_peer_run_done(pool)) != FHS_OK) break;
         if (timed) fhs_ctx_timer_stop(ctx);
         if (n_out && out_host) {
             if (fhs_host_is_pinned(out_host)) {
@@ -528,6 +538,7 @@ extern "C" int fhs_prog_run_ex(const fhs_prog *p, fhs_ctx *ctx, const fhs_operan
     } while (0);
     const int src = fhs_ctx_synchronize(ctx);   // operands (caller memory) and results are settled on return
     if (rc == FHS_OK) rc = src;
+    if (rc == FHS_OK && peer_window) rc = fhs_pool_peer_status(pool);
     if (stats) {
         float dev_ms = 0.f;
         if (!(timed && rc == FHS_OK && fhs_ctx_timer_ms(ctx, &dev_ms) == FHS_OK)) dev_ms = -1.f;

@@ -3,9 +3,27 @@
 //   (bivariate pack 4x+y, compare x-y, block pack 4hi+lo, <=5-term sums, scalar add; replaces the
 //   linear shortint ops tfhe-rs runs before each PBS: unchecked_scalar_mul / unchecked_add / sub),
 //   then keyswitch + blind rotation of the whole level, results written to consecutive pool slots.
+#include <cstring>
+#include <vector>
+
 #include "fhs_internal.cuh"
 
 namespace fhs {
+
+// Control words of a peer window; every word that another GPU writes sits in its own 128-byte line.
+constexpr int kMaxPeers = 8;
+struct PeerCtrl {
+    uint32_t arrive[kMaxPeers][32];   // [q][0]: last step whose blocks from rank q have all landed here
+    uint32_t done[32];                // [0]: runs THIS rank has completed (it no longer reads that run's blocks);
+                                      // the peers poll it over NVLink before the first stores of their next run, so
+                                      // nobody writes into a rank's memory after that rank's last run has ended
+    uint32_t cta_count[32];           // local: CTAs of the current push kernel that have finished their stores
+    uint32_t error[32];               // local: a wait timed out
+};
+struct PeerPtrs {
+    uint64_t *pool[kMaxPeers];
+    PeerCtrl *ctrl[kMaxPeers];
+};
 
 struct Pool {
     Ctx *ctx;
@@ -26,6 +44,18 @@ struct Pool {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t write_done = nullptr;
     bool write_pending = false;
+    // peer window (fhs_pool_create_shared): the pool is a cudaMalloc block followed by a control area, mapped
+    // into every other rank's address space; result blocks of a level that was split by rank are pushed
+    // into the peers' pools by this library's own kernel instead of an NCCL all-gather
+    bool shared = false;            // mapped on every rank
+    bool own_malloc = false;        // p->d came from cudaMalloc (IPC needs that), not from the stream-ordered pool
+    int rank = 0, world = 1;
+    uint64_t *peer_pool[kMaxPeers] = {};
+    PeerCtrl *peer_ctrl[kMaxPeers] = {};
+    uint32_t step = 0, runs = 0;    // sharded levels pushed so far / runs completed (same on every rank)
+    bool first_of_run = true;
+    uint32_t *h_err = nullptr;      // page-locked copy of the control area's error word (valid after a stream sync)
+    unsigned long long pushes = 0;
 };
 
 namespace {
@@ -43,6 +73,69 @@ gather_linear_kernel(const uint64_t *__restrict__ pool, const uint32_t *__restri
             acc += (uint64_t)(int64_t)coef[t] * pool[(size_t)idx[t] * width + j];
         o[j] = acc;
     }
+}
+
+// ---- peer windows: all-gather of a split level's result blocks as ONE kernel over NVLink peer memory ----
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// spin until *p has reached `want` (sequence numbers, wrap-safe); gives up after `timeout` clocks so that a
+// dead peer costs an error code, not a hung GPU
+__device__ __forceinline__ bool wait_reached(const uint32_t *p, uint32_t want, long long timeout, const uint32_t *broken) {
+    if (*reinterpret_cast<const volatile uint32_t *>(broken)) return false;   // an earlier wait timed out: do not wait again
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(p) - want) < 0) {
+        if (clock64() - t0 > timeout) return false;
+        __nanosleep(64);
+    }
+    return true;
+}
+
+// Rank `rank` owns n_words u64 at word_off of its pool (the blocks it has just computed).  Every CTA copies a
+// stride of them into the same place of every peer's pool (plain stores over NVLink), fences, and counts
+// itself; the last CTA publishes `step` in arrive[rank] of every peer and then waits until every peer's
+// `step` has arrived here -- when the kernel ends, the level's blocks of all ranks are in the local pool.
+// need_done != 0 (first split level of a run on a reused pool): wait first until every peer has finished run
+// need_done (polling ITS done word), because it may still be reading the slots these stores overwrite.
+__global__ void __launch_bounds__(256)
+peer_allgather_kernel(PeerPtrs pp, int rank, int world, size_t word_off, size_t n_words, uint32_t step,
+                      uint32_t need_done, long long timeout) {
+    PeerCtrl *mine = pp.ctrl[rank];
+    __shared__ int s_flag;
+    if (need_done) {
+        if (threadIdx.x < world && threadIdx.x != rank && !wait_reached(&pp.ctrl[threadIdx.x]->done[0], need_done, timeout, &mine->error[0]))
+            atomicExch(&mine->error[0], 1u);
+        __syncthreads();
+    }
+    const uint64_t *__restrict__ src = pp.pool[rank] + word_off;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (size_t)gridDim.x * blockDim.x) {
+        const uint64_t v = src[i];
+        for (int d = 1; d < world; d++) {
+            int q = rank + d;
+            if (q >= world) q -= world;
+            pp.pool[q][word_off + i] = v;
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) s_flag = atomicAdd(&mine->cta_count[0], 1u) == gridDim.x - 1 ? 1 : 0;
+    __syncthreads();
+    if (!s_flag) return;
+    if (threadIdx.x == 0) mine->cta_count[0] = 0;       // the next push kernel is stream-ordered after this one
+    __threadfence_system();
+    if (threadIdx.x < world && threadIdx.x != rank) {
+        st_release_sys(&pp.ctrl[threadIdx.x]->arrive[rank][0], step);
+        if (!wait_reached(&mine->arrive[threadIdx.x][0], step, timeout, &mine->error[0])) atomicExch(&mine->error[0], 1u);
+    }
+}
+
+__global__ void peer_done_kernel(PeerCtrl *mine, uint32_t runs) {
+    if (threadIdx.x == 0) st_release_sys(&mine->done[0], runs);
 }
 
 // Pool memory comes from the device's stream-ordered allocator on the context's stream (the default
@@ -119,6 +212,10 @@ void fhs_pool_destroy(fhs_pool *hp) {
     Ctx *c = p->ctx;
     cudaStreamSynchronize(c->stream);
     if (p->copy_stream) { cudaStreamSynchronize(p->copy_stream); cudaStreamDestroy(p->copy_stream); }
+    for (int q = 0; q < fhs::kMaxPeers; q++)
+        if (p->shared && q != p->rank && p->peer_pool[q]) cudaIpcCloseMemHandle(p->peer_pool[q]);
+    if (p->own_malloc) { cudaFree(p->d); p->d = nullptr; }
+    if (p->h_err) cudaFreeHost(p->h_err);
     void *all[] = {p->d, p->d_off, p->d_idx, p->d_lut, p->d_coef, p->d_cst, p->d_tables, p->d_stage,
                    p->r_off, p->r_idx, p->r_lut, p->r_coef, p->r_cst, p->r_tables, p->r_stage};
     for (void *q : all) fhs::pool_free(c, q);
@@ -348,5 +445,149 @@ int fhs_level_run(fhs_pool *hp, size_t row_lo, size_t B, int is_pbs, size_t out_
     return fhs_ks_pbs_batch_dev(reinterpret_cast<fhs_ctx *>(c), p->r_stage, p->r_lut + row_lo, p->r_tables,
                                 p->r_luts, B, dst);
 }
+
+// ---- peer windows (include/fhs_cuda.h "own collective") ------------------------------------------------
+// Collective over the context's communicator: every rank calls it at the same point with the same
+// capacity.  The pool is a cudaMalloc block (legacy CUDA IPC cannot export stream-ordered allocations) whose
+// handle travels through the NCCL communicator once; from then on the ranks exchange result blocks with
+// peer_allgather_kernel.  If any rank cannot export / map (no P2P, IPC closed in the container), all ranks
+// agree to leave the pool unshared and the caller keeps using fhs_comm_allgather.
+int fhs_pool_create_shared(fhs_ctx *h, size_t capacity_blocks, fhs_pool **out) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    if (!c || !out || capacity_blocks == 0) return FHS_ERR_INVALID;
+    if (!c->has_keys) { fhs::set_error("keys not uploaded"); return FHS_ERR_NO_KEYS; }
+    if (!c->nccl_comm || c->comm_world < 2 || c->comm_world > fhs::kMaxPeers || !c->knobs.peer_p2p)
+        return fhs_pool_create(h, capacity_blocks, out);
+    FHS_CUDA(cudaSetDevice(c->device));
+    const int rank = c->comm_rank, world = c->comm_world;
+    const size_t pool_bytes = (capacity_blocks * ((size_t)c->big + 1) * sizeof(uint64_t) + 255) & ~(size_t)255;
+    Pool *p = new Pool();
+    p->ctx = c; p->rank = rank; p->world = world; p->capacity = capacity_blocks;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&p->d), pool_bytes + sizeof(fhs::PeerCtrl));
+    if (e != cudaSuccess) { delete p; return fhs::cuda_fail(e, "cudaMalloc(shared pool)"); }
+    p->own_malloc = true;
+    fhs::PeerCtrl *ctrl = reinterpret_cast<fhs::PeerCtrl *>(reinterpret_cast<uint8_t *>(p->d) + pool_bytes);
+    struct Slot { cudaIpcMemHandle_t handle; uint32_t ok; uint32_t pad[15]; };
+    static_assert(sizeof(Slot) == 128, "handle slot");
+    std::vector<Slot> hs(world);
+    memset(hs.data(), 0, world * sizeof(Slot));
+    Slot *d_slots = nullptr;
+    int rc = FHS_OK;
+    bool agreed = false;
+    do {
+        if ((e = cudaHostAlloc(reinterpret_cast<void **>(&p->h_err), sizeof(uint32_t), cudaHostAllocDefault)) != cudaSuccess) break;
+        *p->h_err = 0;
+        if ((e = cudaMalloc(reinterpret_cast<void **>(&d_slots), world * sizeof(Slot))) != cudaSuccess) break;
+        if ((e = cudaMemsetAsync(ctrl, 0, sizeof(fhs::PeerCtrl), c->stream)) != cudaSuccess) break;
+        // round 1: handles.  round 2: did every rank map every peer?
+        bool mine_ok = cudaIpcGetMemHandle(&hs[rank].handle, p->d) == cudaSuccess;
+        if (!mine_ok) cudaGetLastError();
+        for (int round = 0; round < 2 && rc == FHS_OK; round++) {
+            hs[rank].ok = mine_ok ? 1u : 0u;
+            if ((e = cudaMemcpyAsync(d_slots + rank, &hs[rank], sizeof(Slot), cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) break;
+            if ((rc = fhs_comm_allgather(h, reinterpret_cast<uint64_t *>(d_slots), sizeof(Slot))) != FHS_OK) break;
+            if ((e = cudaMemcpyAsync(hs.data(), d_slots, world * sizeof(Slot), cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) break;
+            if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) break;
+            bool all_ok = true;
+            for (int q = 0; q < world; q++) all_ok = all_ok && hs[q].ok;
+            if (!all_ok) { mine_ok = false; if (round == 1) break; continue; }
+            if (round == 0) {
+                for (int q = 0; q < world && mine_ok; q++) {
+                    if (q == rank) continue;
+                    void *ptr = nullptr;
+                    if (cudaIpcOpenMemHandle(&ptr, hs[q].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                        cudaGetLastError();
+                        mine_ok = false;
+                    } else {
+                        p->peer_pool[q] = static_cast<uint64_t *>(ptr);
+                    }
+                }
+            } else {
+                agreed = true;
+            }
+        }
+    } while (0);
+    if (d_slots) cudaFree(d_slots);
+    if (rc == FHS_OK && e != cudaSuccess) rc = fhs::cuda_fail(e, "fhs_pool_create_shared");
+    if (rc != FHS_OK || !agreed) {
+        for (int q = 0; q < world; q++)
+            if (q != rank && p->peer_pool[q]) { cudaIpcCloseMemHandle(p->peer_pool[q]); p->peer_pool[q] = nullptr; }
+    }
+    if (rc != FHS_OK) { cudaFree(p->d); if (p->h_err) cudaFreeHost(p->h_err); delete p; return rc; }
+    if (agreed) {
+        p->shared = true;
+        p->peer_pool[rank] = p->d;
+        for (int q = 0; q < world; q++)
+            p->peer_ctrl[q] = reinterpret_cast<fhs::PeerCtrl *>(reinterpret_cast<uint8_t *>(p->peer_pool[q]) + pool_bytes);
+    }
+    *out = reinterpret_cast<fhs_pool *>(p);
+    return FHS_OK;
+}
+
+int fhs_pool_is_shared(fhs_pool *hp) { return hp && reinterpret_cast<Pool *>(hp)->shared ? 1 : 0; }
+
+// All-gather of the blocks of one split level: rank q has written slots [slot_base + q*per_rank, +n_q) of its
+// own pool (n_q <= per_rank; this rank's n is my_blocks); afterwards every rank's pool holds all of them.
+// Asynchronous on the context's stream; every rank calls it for the same levels in the same order.
+int fhs_pool_peer_allgather(fhs_pool *hp, size_t slot_base, size_t per_rank, size_t my_blocks) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || !p->shared) { fhs::set_error("pool has no peer window"); return FHS_ERR_COMM; }
+    if (my_blocks > per_rank || slot_base + per_rank * (size_t)p->world > p->capacity) {
+        fhs::set_error("fhs_pool_peer_allgather: slots out of range");
+        return FHS_ERR_INVALID;
+    }
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    const size_t w = (size_t)c->big + 1;
+    fhs::PeerPtrs pp;
+    for (int q = 0; q < fhs::kMaxPeers; q++) { pp.pool[q] = p->peer_pool[q]; pp.ctrl[q] = p->peer_ctrl[q]; }
+    const size_t n_words = my_blocks * w;
+    unsigned grid = (unsigned)((n_words + 4095) / 4096);
+    if (grid < 1) grid = 1;
+    if (grid > 2u * (unsigned)c->sm_count) grid = 2u * (unsigned)c->sm_count;
+    const uint32_t need_done = p->first_of_run ? p->runs : 0u;
+    p->first_of_run = false;
+    p->step++;
+    const long long timeout = (long long)c->knobs.peer_timeout_ms * 2000000ll;   // ~2 GHz
+    fhs::peer_allgather_kernel<<<grid, 256, 0, c->stream>>>(pp, p->rank, p->world, (slot_base + per_rank * (size_t)p->rank) * w,
+                                                             n_words, p->step, need_done, timeout);
+    c->launches++;
+    p->pushes++;
+    c->peer_pushes++;
+    FHS_CUDA(cudaGetLastError());
+    return FHS_OK;
+}
+
+// End of a run on a shared pool: tells the peers that this rank no longer reads the blocks of this run (they may
+// overwrite them with the next run's) and fetches the error word.  Call after the last kernel that reads the pool.
+int fhs_pool_peer_run_done(fhs_pool *hp) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || !p->shared) return FHS_OK;
+    if (p->first_of_run) return FHS_OK;          // no split level ran
+    Ctx *c = p->ctx;
+    FHS_CUDA(cudaSetDevice(c->device));
+    p->runs++;
+    p->first_of_run = true;
+    fhs::peer_done_kernel<<<1, 32, 0, c->stream>>>(p->peer_ctrl[p->rank], p->runs);
+    c->launches++;
+    FHS_CUDA(cudaGetLastError());
+    FHS_CUDA(cudaMemcpyAsync(p->h_err, &p->peer_ctrl[p->rank]->error[0], sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    return FHS_OK;
+}
+
+// After a stream synchronisation: FHS_ERR_COMM if a wait of the last run(s) timed out (a peer died or fell
+// more than FHS_PEER_TIMEOUT_MS behind); the blocks of that run are then not to be trusted.
+int fhs_pool_peer_status(fhs_pool *hp) {
+    Pool *p = reinterpret_cast<Pool *>(hp);
+    if (!p || !p->shared || !p->h_err || *p->h_err == 0) return FHS_OK;
+    fhs::set_error("peer window: a wait for another rank timed out");
+    return FHS_ERR_COMM;
+}
+
+unsigned long long fhs_comm_peer_pushes(fhs_ctx *h) {
+    Ctx *c = reinterpret_cast<Ctx *>(h);
+    return c ? c->peer_pushes : 0ull;
+}
+
 
 }  // extern "C"

@@ -40,6 +40,8 @@ EXPORTS = [
     "fhs_dev_alloc", "fhs_dev_free", "fhs_dev_write", "fhs_dev_read", "fhs_host_alloc", "fhs_host_free",
     "fhs_upload_keys_fmt", "fhs_level_d", "fhs_host_is_pinned", "fhs_ctx_cache_get", "fhs_ctx_cache_put", "fhs_cache_drop_owner",
     "fhs_ctx_cache_stats", "fhs_ctx_cache_limit", "fhs_ctx_timer_start", "fhs_ctx_timer_stop", "fhs_ctx_timer_ms",
+    "fhs_pool_create_shared", "fhs_pool_is_shared", "fhs_pool_peer_allgather", "fhs_pool_peer_run_done",
+    "fhs_pool_peer_status", "fhs_comm_peer_pushes",
 ]
 
 _lib = None
@@ -101,6 +103,8 @@ def load_library():
     L.fhs_host_is_pinned.argtypes = [vp]
     L.fhs_ctx_cache_stats.argtypes = [vp, ctypes.POINTER(sz), ctypes.POINTER(sz)]
     L.fhs_ctx_cache_limit.argtypes = [vp, sz]
+    L.fhs_comm_peer_pushes.argtypes = [vp]
+    L.fhs_comm_peer_pushes.restype = ctypes.c_ulonglong
     _lib = L
     return L
 
@@ -351,6 +355,10 @@ class Engine:
         v = ctypes.c_double()
         self._check(self.L.fhs_measure_fp64_tflops(self.h, ctypes.byref(v)))
         return float(v.value)
+
+    def peer_pushes(self):
+        """Split levels exchanged by the library's own peer-window kernel (0: ncclAllGather or single GPU)."""
+        return int(self.L.fhs_comm_peer_pushes(self.h))
 
     def launch_count(self):
         return int(self.L.fhs_launch_count(self.h))

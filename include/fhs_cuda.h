@@ -263,6 +263,27 @@ void fhs_comm_destroy(fhs_ctx *ctx);
  * [d_base + q*bytes_per_rank, +bytes_per_rank); afterwards all world*bytes_per_rank bytes are equal
  * on every rank.  Used by fhs_prog_run_sharded after every level that was split by rank. */
 int fhs_comm_allgather(fhs_ctx *ctx, uint64_t *d_base, size_t bytes_per_rank);
+/* Peer windows: the library's own collective for the levels a sharded program splits by rank.
+ * fhs_pool_create_shared is fhs_pool_create for a pool that every other rank of the context's communicator maps
+ * into its address space (CUDA IPC over NVLink / NVSwitch peer access; the handles travel through the NCCL
+ * communicator once).  COLLECTIVE: every rank calls it at the same point with the same capacity.  Without a
+ * communicator (or with FHS_COMM_P2P=0, or when any rank cannot export / map the memory) the result is an
+ * ordinary pool: ask fhs_pool_is_shared.
+ * fhs_pool_peer_allgather(pool, slot_base, per_rank, my_blocks): rank q has computed slots
+ * [slot_base + q*per_rank, + n_q) of its own pool (this rank's n is my_blocks <= per_rank); ONE kernel stores them
+ * into the same slots of every peer's pool, publishes a sequence number there and waits for the peers' own, so
+ * that kernels queued behind it see the blocks of all ranks -- the all-gather of fhs_comm_allgather without
+ * NCCL's launch and protocol latency.  Asynchronous on the context's stream; every rank calls it for the same
+ * levels in the same order.  fhs_pool_peer_run_done closes a run (the peers may then overwrite this run's blocks);
+ * fhs_pool_peer_status, after a stream synchronisation, is FHS_ERR_COMM when a wait for another rank timed out
+ * (FHS_PEER_TIMEOUT_MS, default 30 s: a dead peer costs an error, not a hung GPU).  Reference: none -- the
+ * reference is single-process; this replaces rayon's fan-out of a level (src/ciphertext/search.rs:33-41). */
+int fhs_pool_create_shared(fhs_ctx *ctx, size_t capacity_blocks, fhs_pool **out);
+int fhs_pool_is_shared(fhs_pool *pool);
+int fhs_pool_peer_allgather(fhs_pool *pool, size_t slot_base, size_t per_rank, size_t my_blocks);
+int fhs_pool_peer_run_done(fhs_pool *pool);
+int fhs_pool_peer_status(fhs_pool *pool);
+unsigned long long fhs_comm_peer_pushes(fhs_ctx *ctx);   /* peer-window all-gathers launched on this context */
 /* Broadcast of a HOST buffer from `root` (staged through device memory, synchronous): how the
  * server keys made on rank 0 reach the other ranks before each calls fhs_upload_keys. */
 int fhs_comm_broadcast_host(fhs_ctx *ctx, void *host_buf, size_t bytes, int root);

@@ -16,10 +16,13 @@ sys.path.insert(0, ROOT)
 def main():
     import torch
     import torch.distributed as dist
-    from fhe_string_b200.api import ClientKey, _wrap
+    from fhe_string_b200.api import ClientKey, _Out, _wrap
     from fhe_string_b200.engine import Engine, default_params
     from fhe_string_b200.program import Program
 
+    if os.environ.get("FHS_WORKER_DUMP_S"):       # debugging aid: where is a stuck rank?
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["FHS_WORKER_DUMP_S"]), exit=True)
     rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -36,6 +39,13 @@ def main():
     eng.comm_broadcast(bsk)
     eng.upload_keys(prm, ksk, bsk)
 
+    # second context with the peer-window exchange switched off: same ops through ncclAllGather
+    os.environ["FHS_COMM_P2P"] = "0"
+    eng_nccl = Engine(local)
+    del os.environ["FHS_COMM_P2P"]
+    eng_nccl.comm_init_from_torch()
+    eng_nccl.upload_keys(prm, ksk, bsk)
+
     s, pat = "the quick brown fox jumps over the dog", "fox jump"
     cases = [("contains", True), ("find", s.find(pat)), ("split", s.split(pat))]
     ok = True
@@ -48,11 +58,25 @@ def main():
             blocks[:] = np.concatenate([ck.encrypt_str(s, 64).blocks, ck.encrypt_str(pat, None).blocks])
         eng.comm_broadcast(blocks)
         prog = Program(op, n_chars, 0, (), 4, 4 if ck is None else ck.num_blocks_usize)
+        pushes0 = eng.peer_pushes()
         out_native, st = prog.run_sharded(eng, blocks, rank, world)
+        # the same cached execution again (run-to-run handshake of the peer window), and NCCL for reference
+        repeat_same = True
+        best = {"p2p": 1e9, "nccl": 1e9}
+        for _ in range(4):
+            again, st2 = prog.run_sharded(eng, blocks, rank, world)
+            repeat_same &= bool(np.array_equal(again, out_native))
+            best["p2p"] = min(best["p2p"], st2["ms"])
+        pushes = eng.peer_pushes() - pushes0
+        out_nccl, _ = prog.run_sharded(eng_nccl, blocks, rank, world)
+        for _ in range(4):
+            _, st3 = prog.run_sharded(eng_nccl, blocks, rank, world)
+            best["nccl"] = min(best["nccl"], st3["ms"])
+        repeat_same &= bool(np.array_equal(out_nccl, out_native)) and eng_nccl.peer_pushes() == 0
         saved, eng.comm = eng.comm, None          # force the torch callback path
         out_torch, _ = prog.run_sharded(eng, blocks, rank, world)
         eng.comm = saved
-        same = np.array_equal(out_native, out_torch)
+        same = np.array_equal(out_native, out_torch) and repeat_same
         # every rank must hold the same result blocks
         t = torch.from_numpy(out_native.view(np.int64).copy()).cuda()
         ref = t.clone()
@@ -60,9 +84,11 @@ def main():
         same_ranks = bool(torch.equal(t, ref))
         dec_ok = True
         if rank == 0:
-            got = _wrap(prog.desc, out_native, ck.num_blocks_usize).decrypt(ck)
+            got = _wrap(prog.desc, _Out(host=out_native), ck.num_blocks_usize).decrypt(ck)
             dec_ok = got == want
-            report[op] = {"levels": st["levels"], "pbs": st["pbs"], "ms": round(st["ms"], 2), "got": repr(got)[:80]}
+            report[op] = {"levels": st["levels"], "pbs": st["pbs"], "ms": round(st["ms"], 2), "got": repr(got)[:80],
+                          "sharded_levels": st.get("sharded_levels"), "peer_pushes_5_runs": pushes,
+                          "wall_ms_p2p": round(best["p2p"], 3), "wall_ms_nccl": round(best["nccl"], 3)}
         flags = torch.tensor([float(same), float(same_ranks), float(dec_ok)], device="cuda")
         dist.all_reduce(flags, op=dist.ReduceOp.MIN)
         ok &= bool(flags.min().item() == 1.0)
@@ -70,6 +96,8 @@ def main():
             report[op]["flags"] = flags.tolist()
     eng.comm_destroy()
     eng.close()
+    eng_nccl.comm_destroy()
+    eng_nccl.close()
     if rank == 0:
         print("MULTI_GPU_RESULT " + json.dumps({"ok": ok, "world": world, "ops": report}))
     dist.barrier()

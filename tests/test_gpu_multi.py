@@ -37,6 +37,31 @@ def test_comm_world_of_one(keyset):
 
 
 @pytest.mark.gpu
+def test_shared_pool_without_peers_is_an_ordinary_pool(engine):
+    """fhs_pool_create_shared is collective over the context's communicator; with no communicator (or a world of
+    one) it must hand back a plain pool, and the peer entry points must refuse it instead of launching."""
+    import ctypes
+    L = engine.L
+    vp, sz = ctypes.c_void_p, ctypes.c_size_t
+    L.fhs_pool_create_shared.argtypes = [vp, sz, ctypes.POINTER(vp)]
+    L.fhs_pool_is_shared.argtypes = [vp]
+    L.fhs_pool_peer_allgather.argtypes = [vp, sz, sz, sz]
+    L.fhs_pool_peer_run_done.argtypes = [vp]
+    L.fhs_pool_peer_status.argtypes = [vp]
+    L.fhs_pool_destroy.argtypes = [vp]
+    L.fhs_pool_destroy.restype = None
+    L.fhs_pool_capacity.argtypes = [vp]
+    L.fhs_pool_capacity.restype = sz
+    pool = vp()
+    assert L.fhs_pool_create_shared(engine.h, 16, ctypes.byref(pool)) == 0
+    assert L.fhs_pool_capacity(pool) == 16 and L.fhs_pool_is_shared(pool) == 0
+    assert L.fhs_pool_peer_allgather(pool, 0, 2, 2) == -5          # FHS_ERR_COMM: no peer window
+    assert L.fhs_pool_peer_run_done(pool) == 0 and L.fhs_pool_peer_status(pool) == 0
+    assert engine.peer_pushes() == 0
+    L.fhs_pool_destroy(pool)
+
+
+@pytest.mark.gpu
 def test_sharded_string_ops_native_exchange_two_gpus():
     import torch
     if torch.cuda.device_count() < 2:
