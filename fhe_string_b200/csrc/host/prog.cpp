@@ -1,7 +1,9 @@
 // fhs_prog: build / export / run level programs (include/fhs_string.h).
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -291,6 +293,165 @@ static void level_slice(size_t B, int rank, int world, size_t shard_min, size_t 
     *hi = std::min(B, *per * (size_t)(rank + 1));
 }
 
+// ---- level balancing ---------------------------------------------------------------------------------
+// A level costs what its WAVES cost, not what its evaluations cost: on a B200 (148 SMs) one blind-rotation
+// wave takes 1.65 ms for up to 74 ciphertexts (pair kernel), 2.3 ms up to 148 and 3.6 ms up to 296 (wide
+// kernel), 5.28 ms up to 370 (wide + pair) and 5.9 ms per round of 592 (throughput kernel); measured, DESIGN.md
+// section 4.  "As soon as possible" levels therefore waste time whenever a level sits just above a wave
+// boundary while some of its evaluations are not needed until later.  balance_levels keeps the depth and moves
+// evaluations with slack to the next level where that lowers the modelled time of the two levels, a few
+// sweeps front to back.  Every rank runs the same deterministic pass on the same graph, so the plans agree.
+static double wave_ms(size_t b) {
+    if (b == 0) return 0.0;
+    const size_t full = b / 592, r = b % 592;
+    double t = 5.9 * (double)full;
+    if (r == 0) t += 0.0;
+    else if (r <= 74) t += 1.65;
+    else if (r <= 148) t += 2.3;
+    else if (r <= 296) t += 3.6;
+    else if (r <= 370) t += 5.28;
+    else t += 5.9;
+    return t + 0.07;            // gather + keyswitch launches of the level
+}
+static double level_ms(size_t B, int world, size_t shard_min) {
+    if (world <= 1 || B <= shard_min) return wave_ms(B);
+    return wave_ms((B + world - 1) / world) + 0.02;   // + exchange
+}
+
+// returns the level of every node (inputs 0), starting from the levels the graph builder assigned
+static std::vector<int32_t> balance_levels(const Graph &g, int world, size_t shard_min) {
+    const size_t N = g.nodes.size();
+    std::vector<int32_t> asap(N);
+    for (size_t i = 0; i < N; i++) asap[i] = g.nodes[i].level;
+    const int D = g.depth();
+    const char *knob = getenv("FHS_LEVEL_BALANCE");
+    if ((knob && atoi(knob) == 0) || D < 2) return asap;
+    // LUT evaluations that read node i, directly or through linear nodes (nodes are in topological order)
+    std::vector<std::vector<int32_t>> readers(N);
+    for (size_t c = N; c-- > 0;) {
+        const Node &n = g.nodes[c];
+        for (uint32_t t = n.t0; t < n.t0 + n.tn; t++) {
+            std::vector<int32_t> &r = readers[(size_t)g.terms[t].src];
+            if (n.kind == K_PBS) r.push_back((int32_t)c);
+            else r.insert(r.end(), readers[c].begin(), readers[c].end());
+        }
+    }
+    for (auto &r : readers) { std::sort(r.begin(), r.end()); r.erase(std::unique(r.begin(), r.end()), r.end()); }
+    const size_t unit = world > 1 ? (size_t)world : 1;
+    auto targets = [&](size_t b) {
+        std::vector<size_t> v;
+        static const size_t tiers[5] = {74, 148, 296, 370, 592};
+        for (size_t th : tiers)
+            for (size_t k = 0; k < 8; k++) {
+                const size_t x = (th + 592 * k) * unit;
+                if (x < b) v.push_back(x);
+            }
+        if (unit > 1 && shard_min < b) v.push_back(shard_min);
+        v.push_back(0);
+        return v;
+    };
+    auto total_ms = [&](const std::vector<int32_t> &lvl) {
+        std::vector<size_t> cnt(D + 2, 0);
+        for (size_t i = 0; i < N; i++) if (g.nodes[i].kind == K_PBS) cnt[lvl[i]]++;
+        double t = 0;
+        for (int l = 1; l <= D; l++) t += level_ms(cnt[l], world, shard_min);
+        return t;
+    };
+    // one strategy: sweeps over the levels (front to back, or back to front so that readers make room first);
+    // an evaluation may move from level l to l + 1 when every LUT that reads it runs at l + 2 or later
+    auto run = [&](bool back_first) {
+        std::vector<int32_t> lvl = asap;
+        std::vector<std::vector<int32_t>> at(D + 2);
+        for (size_t i = 0; i < N; i++)
+            if (g.nodes[i].kind == K_PBS) at[lvl[i]].push_back((int32_t)i);
+        for (int sweep = 0; sweep < 6; sweep++) {
+            bool any = false;
+            for (int step = 1; step < D; step++) {
+                const int l = back_first ? D - step : step;
+                std::vector<int32_t> &cur = at[l], &nxt = at[l + 1];
+                const size_t b = cur.size();
+                if (b == 0) continue;
+                std::vector<int32_t> mv;
+                for (int32_t i : cur) {
+                    bool free_to_move = true;
+                    for (int32_t c : readers[i]) if (lvl[c] < l + 2) { free_to_move = false; break; }
+                    if (free_to_move) mv.push_back(i);
+                }
+                if (mv.empty()) continue;
+                const double before = level_ms(b, world, shard_min) + level_ms(nxt.size(), world, shard_min);
+                double best = 1e-9;
+                size_t best_k = 0;
+                for (size_t tgt : targets(b)) {
+                    const size_t k = b - tgt;
+                    if (k == 0 || k > mv.size()) continue;
+                    const double gain = before - level_ms(b - k, world, shard_min) - level_ms(nxt.size() + k, world, shard_min);
+                    if (gain > best) { best = gain; best_k = k; }
+                }
+                if (!best_k) continue;
+                mv.resize(best_k);                      // ascending node ids
+                std::vector<int32_t> keep;
+                keep.reserve(b - best_k);
+                for (int32_t i : cur)
+                    if (!std::binary_search(mv.begin(), mv.end(), i)) keep.push_back(i);
+                for (int32_t i : mv) { lvl[i] = l + 1; nxt.push_back(i); }
+                std::sort(nxt.begin(), nxt.end());      // execution order inside a level stays the node order
+                cur.swap(keep);
+                any = true;
+            }
+            if (!any) break;
+        }
+        return lvl;
+    };
+    std::vector<int32_t> lvl = asap;
+    double best_ms = total_ms(asap);
+    for (int strategy = 0; strategy < 2; strategy++) {
+        std::vector<int32_t> cand = run(strategy == 1);
+        const double ms = total_ms(cand);
+        if (ms < best_ms - 1e-9) { best_ms = ms; lvl.swap(cand); }
+    }
+    // linear nodes follow their sources; then check every edge (fall back to the builder's levels on any doubt)
+    for (size_t i = 0; i < N; i++) {
+        const Node &n = g.nodes[i];
+        if (n.kind != K_LIN) continue;
+        int32_t l = 0;
+        for (uint32_t t = n.t0; t < n.t0 + n.tn; t++) l = std::max(l, lvl[g.terms[t].src]);
+        lvl[i] = l;
+    }
+    bool ok = true;
+    for (size_t i = 0; i < N && ok; i++) {
+        const Node &n = g.nodes[i];
+        for (uint32_t t = n.t0; t < n.t0 + n.tn && ok; t++) {
+            const int32_t ls = lvl[g.terms[t].src];
+            ok = n.kind == K_PBS ? ls < lvl[i] : ls <= lvl[i];
+        }
+        ok = ok && lvl[i] <= D;
+    }
+    if (getenv("FHS_BALANCE_DEBUG"))
+        fprintf(stderr, "balance_levels: world %d, %zu nodes, depth %d: %.2f -> %.2f ms (model)%s\n", world, N, D,
+                total_ms(asap), best_ms, ok ? "" : "  INVALID, falling back");
+    return ok ? lvl : asap;
+}
+
+// The level every node runs at on `world` GPUs after balance_levels (what build_exec executes), and the
+// modelled time of the as-soon-as-possible and of the balanced schedule: for tests and for tools.
+extern "C" int fhs_prog_export_schedule(const fhs_prog *p, int world, size_t shard_min, int32_t *level, double model_ms[2]) {
+    if (!p || !level || world < 1) return FHS_ERR_INVALID;
+    if (shard_min == 0) shard_min = 74;
+    const Graph &g = p->g;
+    const std::vector<int32_t> lvl = balance_levels(g, world, shard_min);
+    const int D = g.depth();
+    std::vector<size_t> c0(D + 2, 0), c1(D + 2, 0);
+    for (size_t i = 0; i < g.nodes.size(); i++) {
+        level[i] = lvl[i];
+        if (g.nodes[i].kind == K_PBS) { c0[g.nodes[i].level]++; c1[lvl[i]]++; }
+    }
+    if (model_ms) {
+        model_ms[0] = model_ms[1] = 0.0;
+        for (int l = 1; l <= D; l++) { model_ms[0] += level_ms(c0[l], world, shard_min); model_ms[1] += level_ms(c1[l], world, shard_min); }
+    }
+    return FHS_OK;
+}
+
 extern "C" int fhs_prog_plan(const fhs_prog *p, int rank, int world, size_t shard_min, uint64_t *levels_out,
                              size_t cap_levels, size_t *n_levels) {
     // levels_out[4*l + {0,1,2,3}] = B, blocks per rank (0 = replicated), lo, hi of this rank
@@ -298,10 +459,12 @@ extern "C" int fhs_prog_plan(const fhs_prog *p, int rank, int world, size_t shar
     const Graph &g = p->g;
     const int D = g.depth();
     std::vector<size_t> cnt(D + 1, 0);
-    for (auto &n : g.nodes) if (n.kind == K_PBS) cnt[n.level]++;
+    const std::vector<int32_t> lvl = balance_levels(g, world, shard_min ? shard_min : 74);
+    for (size_t i = 0; i < g.nodes.size(); i++) if (g.nodes[i].kind == K_PBS) cnt[lvl[i]]++;
     size_t k = 0;
     for (int l = 1; l <= D; l++) {
         size_t per, lo, hi;
+        if (cnt[l] == 0) continue;          // a level the balancing pass emptied
         level_slice(cnt[l], rank, world, shard_min, &per, &lo, &hi);
         if (levels_out && k < cap_levels) { levels_out[4 * k] = cnt[l]; levels_out[4 * k + 1] = per; levels_out[4 * k + 2] = lo; levels_out[4 * k + 3] = hi; }
         k++;
@@ -347,9 +510,10 @@ int build_exec(const fhs_prog *p, fhs_ctx *ctx, int rank, int world, size_t shar
     // slots: inputs first, then per level the PBS nodes, then the linear outputs of that level,
     // finally the program outputs gathered into consecutive slots (one read-back at the end)
     std::vector<std::vector<int32_t>> pbs_at(D + 1), lin_at(D + 1);
+    const std::vector<int32_t> lvl = balance_levels(g, world, shard_min);
     for (size_t i = 0; i < N; i++) {
-        if (g.nodes[i].kind == K_PBS) pbs_at[g.nodes[i].level].push_back((int32_t)i);
-        else if (g.nodes[i].kind == K_LIN) lin_at[g.nodes[i].level].push_back((int32_t)i);
+        if (g.nodes[i].kind == K_PBS) pbs_at[lvl[i]].push_back((int32_t)i);
+        else if (g.nodes[i].kind == K_LIN) lin_at[lvl[i]].push_back((int32_t)i);
     }
     std::vector<uint32_t> slot(N, 0);
     size_t next = 0;

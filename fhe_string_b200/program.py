@@ -38,6 +38,7 @@ def load_host_library():
     L.fhs_prog_run_many.argtypes = [vp, vp, sz, vp, vp, vp]
     L.fhs_prog_run_sharded.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, sz, vp, vp]
     L.fhs_prog_plan.argtypes = [vp, ctypes.c_int, ctypes.c_int, sz, vp, sz, ctypes.POINTER(sz)]
+    L.fhs_prog_export_schedule.argtypes = [vp, ctypes.c_int, sz, vp, vp]
     _lib = L
     return L
 
@@ -162,6 +163,14 @@ class Program:
         if rc != 0:
             raise FhsError("fhs_prog_plan failed")
         return buf[: 4 * n.value].reshape(-1, 4)
+
+    def schedule(self, world=1, shard_min=74):
+        """(level per node as executed on `world` GPUs, modelled ms of the ASAP schedule, of the balanced one)."""
+        lvl = np.zeros(self.n_nodes, dtype=np.int32)
+        ms = np.zeros(2, dtype=np.float64)
+        if self.L.fhs_prog_export_schedule(self.h, int(world), int(shard_min), lvl.ctypes.data, ms.ctypes.data) != 0:
+            raise FhsError("fhs_prog_export_schedule failed")
+        return lvl, float(ms[0]), float(ms[1])
 
     def run_sharded(self, engine, in_blocks, rank, world, shard_min=74):
         """One process per GPU; every rank passes the same inputs.  Levels are split by rank and

@@ -61,6 +61,13 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
 int fhs_prog_export_ranges(const fhs_prog *p, int32_t *in_lo, int32_t *in_hi, int32_t *out_lo, int32_t *out_hi,
                            uint8_t *signed_in);
 
+/* Schedule the executor uses on `world` GPUs (shard_min 0 = 74): level[node] after the level-balancing pass
+ * (a level costs what its blind-rotation WAVES cost -- 74 / 148 / 296 / 370 / 592 ciphertexts on a B200 -- so
+ * evaluations with slack move to the next level where that saves a wave; depth and results are unchanged), and
+ * model_ms = {as-soon-as-possible, balanced} modelled device time.  FHS_LEVEL_BALANCE=0 switches the pass off.
+ * Replaces nothing in the reference (rayon runs each op's PBS as they come); for tests and tools. */
+int fhs_prog_export_schedule(const fhs_prog *p, int world, size_t shard_min, int32_t *level, double model_ms[2]);
+
 /* Execute on the GPU: in_blocks [n_inputs][k*N+1] host -> out_blocks [n_outputs][k*N+1] host.
  * Ciphertexts stay in a device pool between levels.  stats[0..3] (may be NULL) = levels run,
  * LUT evaluations, kernels launched, device milliseconds (events around the whole program). */

@@ -1,0 +1,70 @@
+"""Level balancing (csrc/host/prog.cpp balance_levels): a level costs what its blind-rotation waves cost, so
+evaluations with slack are moved to later levels when that saves a wave.  Checked on CPU for every op family:
+the schedule the executor runs respects every data dependency, keeps depth and evaluation count, is never
+modelled slower than the as-soon-as-possible one, is the same on every rank, and is a real gain on the ops
+BASELINE names (split / replace)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from fhe_string_b200.program import Program
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+CASES = [
+    ("eq", (65, 65), {}), ("lt", (65, 65), {}), ("contains", (65, 9), {}), ("find", (65, 9), {}),
+    ("rfind", (65, 9), {}), ("trim", (65,), {}), ("split", (65, 9), {}), ("rsplit", (33, 3), {}),
+    ("split", (257, 2), dict(num_blocks_usize=5)), ("to_uppercase", (257,), dict(num_blocks_usize=5)),
+    ("replace", (65, 3, 2), dict(scalars=(64,))), ("strip_prefix", (33, 5), {}),
+]
+
+
+def _check(prog, world):
+    d = prog.export()
+    lvl, asap_ms, bal_ms = prog.schedule(world)
+    kind, t0, tn, src = d["kind"], d["t0"], d["tn"], d["term_src"]
+    assert bal_ms <= asap_ms + 1e-9
+    assert lvl.max() <= prog.depth and np.all(lvl[kind == 0] == 0)
+    for i in range(prog.n_nodes):
+        s = src[t0[i]:t0[i] + tn[i]]
+        if kind[i] == 1:
+            assert np.all(lvl[s] < lvl[i]), f"LUT {i} at level {lvl[i]} reads level {lvl[s].max()}"
+            assert lvl[i] >= d["level"][i]                    # never earlier than its inputs allow
+        elif kind[i] == 2 and len(s):
+            assert lvl[i] == lvl[s].max()
+    assert int((kind == 1).sum()) == prog.pbs_count
+    # the plan (what fhs_prog_run_ex executes and what the ranks split) is this schedule
+    plan = prog.plan(0, world)
+    sizes = np.bincount(lvl[kind == 1], minlength=prog.depth + 1)[1:]
+    assert [int(x) for x in plan[:, 0]] == [int(x) for x in sizes if x]
+    return asap_ms, bal_ms
+
+
+@pytest.mark.parametrize("op,n_chars,kw", CASES)
+def test_balanced_schedule_is_valid_and_not_slower(op, n_chars, kw):
+    prog = Program(op, n_chars=n_chars, **kw)
+    for world in (1, 2, 8):
+        _check(prog, world)
+    # every rank of a world derives the same levels (the pass does not look at the rank)
+    a = prog.plan(0, 4)
+    b = prog.plan(3, 4)
+    assert np.array_equal(a[:, :2], b[:, :2])
+
+
+def test_balancing_gains_on_the_baseline_ops():
+    split64 = Program("split", n_chars=(65, 9))
+    split256 = Program("split", n_chars=(257, 2), num_blocks_usize=5)
+    for prog, world, want in ((split64, 1, 0.06), (split256, 1, 0.08), (split256, 2, 0.08), (split64, 8, 0.02)):
+        asap_ms, bal_ms = _check(prog, world)
+        assert bal_ms <= (1 - want) * asap_ms, (prog.op, world, asap_ms, bal_ms)
+
+
+def test_balancing_can_be_switched_off():
+    code = ("from fhe_string_b200.program import Program; p = Program('split', n_chars=(65, 9)); "
+            "import numpy as np; l, a, b = p.schedule(1); print(int(np.array_equal(l, p.export()['level'])), a == b)")
+    env = dict(os.environ, FHS_LEVEL_BALANCE="0", PYTHONPATH=ROOT)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=120)
+    assert out.stdout.split() == ["1", "True"], (out.stdout, out.stderr[-500:])
