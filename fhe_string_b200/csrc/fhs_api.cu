@@ -102,6 +102,7 @@ static void read_knobs(Ctx *c) {
     c->knobs.ks_variant = (int)env_int("FHS_KS_VARIANT", 3);
     c->knobs.ks_umma_min = (int)env_int("FHS_KS_UMMA_MIN", 1);
     c->knobs.ks_mma_min = (int)env_int("FHS_KS_MMA_MIN", 1);
+    c->knobs.ks_splitk = (int)env_int("FHS_KS_SPLITK", 1);
     c->knobs.bsk_f64 = env_int("FHS_BSK_XF", 1) == 0;
     c->knobs.ks_baseline_keys = c->knobs.ks_variant != 3 || c->knobs.ks_umma_min > 1;
     c->knobs.peer_p2p = (int)env_int("FHS_COMM_P2P", 1);

@@ -43,6 +43,7 @@ struct Ctx {
         int ks_variant = 3;        // FHS_KS_VARIANT: 3 tcgen05 (default), 2 mma.sync baseline, 1 IMAD baseline
         int ks_umma_min = 1;       // FHS_KS_UMMA_MIN
         int ks_mma_min = 1;        // FHS_KS_MMA_MIN
+        int ks_splitk = 1;         // FHS_KS_SPLITK=0: no split-K in the tcgen05 keyswitch at small batches
         int bsk_f64 = 0;           // FHS_BSK_XF=0: plain f64 key transform instead of double-double
         int ks_baseline_keys = 0;  // key forms of the baseline keyswitch kernels are resident (variant != 3)
         int peer_p2p = 1;          // FHS_COMM_P2P=0: sharded levels exchange with ncclAllGather instead of the peer-window kernel

@@ -47,10 +47,15 @@ __device__ __forceinline__ void signed_digits(uint64_t x, int (&d)[kLv]) {
 }
 
 // masks -> digit tiles.  grid (n_kb, m_tiles), 256 threads: item q = tid + 256 r: row q >> 3, mask
-// elements 4 (q & 7) .. +3 of K-block kb.  Rows past the batch are zero.
+// elements 4 (q & 7) .. +3 of K-block kb.  Rows past the batch are zero.  zero_out / zero_words: see below.
 __global__ void __launch_bounds__(256)
-ks_digits_kernel(const uint64_t *__restrict__ in, uint8_t *__restrict__ at, unsigned int batch, int big, int n_kb) {
+ks_digits_kernel(const uint64_t *__restrict__ in, uint8_t *__restrict__ at, unsigned int batch, int big, int n_kb,
+                 uint64_t *__restrict__ zero_out, size_t zero_words) {
     const int kb = blockIdx.x, m_tile = blockIdx.y, tid = threadIdx.x;
+    // split-K keyswitch (small batches): the partial sums are added into `out` atomically, so it starts at zero
+    for (size_t i = ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 256 + tid; i < zero_words;
+         i += (size_t)gridDim.x * gridDim.y * 256)
+        zero_out[i] = 0ull;
     uint8_t *dst = at + ((size_t)m_tile * n_kb + kb) * kAStage;
     const size_t in_w = (size_t)big + 1;
 #pragma unroll
@@ -114,12 +119,17 @@ constexpr uint32_t kIdesc = (2u << 4) | (1u << 7) | (0u << 10) | ((uint32_t)(kUN
 __global__ void __launch_bounds__(kThreadsU, 1)
 keyswitch_umma_kernel(const uint8_t *__restrict__ at, const uint8_t *__restrict__ ku,
                       const uint64_t *__restrict__ in, uint64_t *__restrict__ out, unsigned int batch,
-                      int n_small, int big, int n_kb) {
+                      int n_small, int big, int n_kb, int ksplit) {
     extern __shared__ __align__(1024) unsigned char smem[];
     __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], accum_bar;
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int n_tile = blockIdx.x, m_tile = blockIdx.y;
+    // split-K (levels of a few ciphertexts: 24 column tiles would leave 124 SMs idle, each streaming 3.8 MB of key
+    // at one SM's L2 bandwidth): CTA z of ksplit takes K-blocks [kb0, kb1) and adds its partial sums atomically
+    // (wrapping u64 adds commute, so the result is the same bits whatever the order)
+    const int kb0 = (int)(((long)blockIdx.z * n_kb) / ksplit), kb1 = (int)(((long)(blockIdx.z + 1) * n_kb) / ksplit);
+    const int my_kb = kb1 - kb0;
     unsigned char *As = smem;                          // kStages x 20 KB
     unsigned char *Bs = smem + kStages * kAStage;      // kStages x 40 KB
 
@@ -141,8 +151,9 @@ keyswitch_umma_kernel(const uint8_t *__restrict__ at, const uint8_t *__restrict_
         // producer: one bulk copy per operand per K-block
         const uint8_t *a_src = at + (size_t)m_tile * n_kb * kAStage;
         const uint8_t *b_src = ku + (size_t)n_tile * n_kb * kBStage;
-        for (int kb = 0; kb < n_kb; kb++) {
-            const int s = kb % kStages, it = kb / kStages;
+        for (int kk = 0; kk < my_kb; kk++) {
+            const int kb = kb0 + kk;
+            const int s = kk % kStages, it = kk / kStages;
             if (it > 0) mbar_wait(smem_u32(&empty_bar[s]), (uint32_t)((it - 1) & 1));
             if (lane == 0) {
                 const uint32_t bar = smem_u32(&full_bar[s]);
@@ -156,8 +167,8 @@ keyswitch_umma_kernel(const uint8_t *__restrict__ at, const uint8_t *__restrict_
         }
     } else if (warp == 1) {
         // MMA issuer: 5 levels per K-block, each M128 N256 K32, accumulating into TMEM columns 0..255
-        for (int kb = 0; kb < n_kb; kb++) {
-            const int s = kb % kStages, it = kb / kStages;
+        for (int kk = 0; kk < my_kb; kk++) {
+            const int s = kk % kStages, it = kk / kStages;
             mbar_wait(smem_u32(&full_bar[s]), (uint32_t)(it & 1));
             tmem_fence_after_sync();
             if (lane == 0) {
@@ -165,7 +176,7 @@ keyswitch_umma_kernel(const uint8_t *__restrict__ at, const uint8_t *__restrict_
 #pragma unroll
                 for (int t = 0; t < kLv; t++) {
                     const uint64_t da = umma_desc(a0 + t * (kUM * kUK)), db = umma_desc(b0 + t * (kUN * kUK));
-                    const uint32_t accumulate = (kb > 0 || t > 0) ? 1u : 0u;
+                    const uint32_t accumulate = (kk > 0 || t > 0) ? 1u : 0u;
                     asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
                                  "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}"
                                  ::"r"(tmem_base), "l"(da), "l"(db), "r"(kIdesc), "r"(accumulate) : "memory");
@@ -173,7 +184,7 @@ keyswitch_umma_kernel(const uint8_t *__restrict__ at, const uint8_t *__restrict_
                 // frees the smem slot once these MMAs have read it (implies fence::before_thread_sync)
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                              ::"r"(smem_u32(&empty_bar[s])) : "memory");
-                if (kb == n_kb - 1)
+                if (kk == my_kb - 1)
                     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                                  ::"r"(smem_u32(&accum_bar)) : "memory");
             }
@@ -201,8 +212,9 @@ keyswitch_umma_kernel(const uint8_t *__restrict__ at, const uint8_t *__restrict_
                 for (int l = 0; l < 8; l++) v += (uint64_t)(int64_t)(int32_t)r[e * 8 + l] << (8 * l);
                 const int j = n_tile * (kUN / 8) + c4 * 4 + e;
                 if (ct < batch && j < out_w) {
-                    const uint64_t body = (j == n_small) ? in[(size_t)ct * in_w + big] : 0ull;
-                    out[(size_t)ct * out_w + j] = body - v;
+                    const uint64_t body = (j == n_small && blockIdx.z == 0) ? in[(size_t)ct * in_w + big] : 0ull;
+                    if (ksplit == 1) out[(size_t)ct * out_w + j] = body - v;
+                    else atomicAdd(reinterpret_cast<unsigned long long *>(out + (size_t)ct * out_w + j), (unsigned long long)(body - v));
                 }
             }
         }
@@ -246,12 +258,20 @@ int launch_keyswitch_umma(Ctx *c, const uint64_t *d_in, size_t batch, uint64_t *
         FHS_CUDA(cudaMalloc(&c->d_ks_digits, need));
         c->cap_digits = need;
     }
-    ks_digits_kernel<<<dim3(n_kb, m_tiles), 256, 0, c->stream>>>(d_in, c->d_ks_digits, (unsigned int)batch, (int)c->big, n_kb);
+    const int n_tiles = (int)(((size_t)(c->n + 1) * 8 + kUN - 1) / kUN);
+    // split-K while the column x row tiles alone would leave more than half of the SMs idle
+    int ksplit = 1;
+    if (c->knobs.ks_splitk) {
+        ksplit = c->sm_count / (n_tiles * (int)m_tiles);
+        if (ksplit > 8) ksplit = 8;
+        if (ksplit < 2) ksplit = 1;
+    }
+    ks_digits_kernel<<<dim3(n_kb, m_tiles), 256, 0, c->stream>>>(d_in, c->d_ks_digits, (unsigned int)batch, (int)c->big, n_kb,
+                                                                 d_small, ksplit > 1 ? batch * ((size_t)c->n + 1) : 0);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
-    const int n_tiles = (int)(((size_t)(c->n + 1) * 8 + kUN - 1) / kUN);
-    keyswitch_umma_kernel<<<dim3(n_tiles, m_tiles), kThreadsU, smem_bytes, c->stream>>>(
-        c->d_ks_digits, c->d_ksk_u, d_in, d_small, (unsigned int)batch, (int)c->n, (int)c->big, n_kb);
+    keyswitch_umma_kernel<<<dim3(n_tiles, m_tiles, ksplit), kThreadsU, smem_bytes, c->stream>>>(
+        c->d_ks_digits, c->d_ksk_u, d_in, d_small, (unsigned int)batch, (int)c->n, (int)c->big, n_kb, ksplit);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     return FHS_OK;
@@ -329,12 +349,12 @@ extern "C" int fhs_ks_pbs_batch_dev_noalloc(fhs_ctx *h, const uint64_t *d_in, co
     }
     const int n_kb = (int)kNoAllocKb;
     const unsigned m_tiles = (unsigned)((batch + kUM - 1) / kUM);
-    ks_digits_kernel<<<dim3(n_kb, m_tiles), 256, 0, c->stream>>>(d_in, digits, (unsigned int)batch, (int)c->big, n_kb);
+    ks_digits_kernel<<<dim3(n_kb, m_tiles), 256, 0, c->stream>>>(d_in, digits, (unsigned int)batch, (int)c->big, n_kb, nullptr, 0);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     const int n_tiles = (int)(((size_t)(c->n + 1) * 8 + kUN - 1) / kUN);
     keyswitch_umma_kernel<<<dim3(n_tiles, m_tiles), kThreadsU, smem_bytes, c->stream>>>(
-        digits, c->d_ksk_u, d_in, small, (unsigned int)batch, (int)c->n, (int)c->big, n_kb);
+        digits, c->d_ksk_u, d_in, small, (unsigned int)batch, (int)c->n, (int)c->big, n_kb, 1);
     c->launches++;
     FHS_CUDA(cudaGetLastError());
     return launch_blind_rotate(c, small, d_lut_id, d_tables, n_luts, batch, d_out);
