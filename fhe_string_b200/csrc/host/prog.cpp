@@ -311,7 +311,7 @@ static double wave_ms(size_t b) {
     else if (r <= 296) t += 3.6;
     else if (r <= 370) t += 5.28;
     else t += 5.9;
-    return t + 0.07;            // gather + keyswitch launches of the level
+    return t + 0.05;            // gather + digit + keyswitch launches of the level
 }
 static double level_ms(size_t B, int world, size_t shard_min) {
     if (world <= 1 || B <= shard_min) return wave_ms(B);
