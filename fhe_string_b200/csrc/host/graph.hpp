@@ -11,6 +11,7 @@
 #include <array>
 #include <cstdio>
 #include <cstdint>
+#include <algorithm>
 #include <map>
 #include <stdexcept>
 #include <string>
@@ -51,6 +52,15 @@ public:
     std::vector<Term> terms;
     std::vector<Table> luts;
     std::map<Table, int> lut_index;
+    std::map<std::vector<int64_t>, Val> cse;   // (kind, table, signedness, constant, sorted terms) -> node
+    static std::vector<int64_t> cse_key(Kind kind, int lut_id, bool signed_in, const Lin &e) {
+        std::vector<std::pair<Val, int32_t>> ts;
+        for (auto &x : e.t) ts.emplace_back(x.src, x.coef);
+        std::sort(ts.begin(), ts.end());
+        std::vector<int64_t> key{(int64_t)kind, (int64_t)lut_id, signed_in ? 1 : 0, e.c};
+        for (auto &x : ts) { key.push_back(x.first); key.push_back(x.second); }
+        return key;
+    }
     float max_input_noise = 0.f;   // largest variance multiplier fed to any PBS
     int64_t pbs_count = 0;
 
@@ -93,6 +103,19 @@ public:
             return constant(v);
         }
         int id = lut_fn(f);
+        // common-subexpression elimination: the same table on the same linear combination is one evaluation
+        // (the builders ask again for zero masks, equality bits, ... from several helpers: 35 % of split-256)
+        std::vector<int64_t> key = cse_key(K_PBS, id, signed_in, e);
+        auto hit = cse.find(key);
+        if (hit != cse.end()) {
+            Node &old = nodes[hit->second];
+            old.lo = std::max(old.lo, (int32_t)out_lo);     // both callers' bounds hold for the one value
+            old.hi = std::min(old.hi, (int32_t)out_hi);
+            old.in_lo = std::max(old.in_lo, e.lo);
+            old.in_hi = std::min(old.in_hi, e.hi);
+            return leaf(hit->second, out_lo, out_hi, 1.f);
+        }
+        cse.emplace(std::move(key), (Val)nodes.size());
         Node n{K_PBS, id, (uint32_t)terms.size(), (uint32_t)e.t.size(), e.c, level_of(e) + 1, out_lo, out_hi};
         n.in_lo = e.lo; n.in_hi = e.hi; n.signed_in = signed_in ? 1 : 0;
         terms.insert(terms.end(), e.t.begin(), e.t.end());
@@ -113,11 +136,45 @@ public:
     // Force `e` to exist as one ciphertext (outputs of an operation).
     Val materialize(const Lin &e) {
         if (e.t.size() == 1 && e.t[0].coef == 1 && e.c == 0) return e.t[0].src;
+        std::vector<int64_t> key = cse_key(K_LIN, -1, false, e);
+        auto hit = cse.find(key);
+        if (hit != cse.end()) return hit->second;
+        cse.emplace(std::move(key), (Val)nodes.size());
         Node n{K_LIN, -1, (uint32_t)terms.size(), (uint32_t)e.t.size(), e.c, level_of(e), e.lo, e.hi};
         n.in_lo = e.lo; n.in_hi = e.hi;
         terms.insert(terms.end(), e.t.begin(), e.t.end());
         nodes.push_back(n);
         return (Val)nodes.size() - 1;
+    }
+    // Drops every node no output depends on (inputs stay: their order is the operand layout) and renumbers;
+    // `outputs` holds node ids (>= 0) or encoded constants (< 0) and is rewritten in place.
+    size_t prune(std::vector<int64_t> &outputs) {
+        const size_t N = nodes.size();
+        std::vector<char> live(N, 0);
+        for (size_t i = 0; i < N; i++) if (nodes[i].kind == K_INPUT) live[i] = 1;
+        for (int64_t o : outputs) if (o >= 0) live[(size_t)o] = 1;
+        for (size_t i = N; i-- > 0;) {
+            if (!live[i]) continue;
+            for (uint32_t t = nodes[i].t0; t < nodes[i].t0 + nodes[i].tn; t++) live[(size_t)terms[t].src] = 1;
+        }
+        std::vector<Val> renum(N, -1);
+        std::vector<Node> nn;
+        std::vector<Term> nt;
+        size_t dropped = 0;
+        for (size_t i = 0; i < N; i++) {
+            if (!live[i]) { dropped++; if (nodes[i].kind == K_PBS) pbs_count--; continue; }
+            Node n = nodes[i];
+            const uint32_t t0 = (uint32_t)nt.size();
+            for (uint32_t t = n.t0; t < n.t0 + n.tn; t++) nt.push_back(Term{renum[(size_t)terms[t].src], terms[t].coef});
+            n.t0 = t0;
+            renum[i] = (Val)nn.size();
+            nn.push_back(n);
+        }
+        nodes.swap(nn);
+        terms.swap(nt);
+        for (int64_t &o : outputs) if (o >= 0) o = renum[(size_t)o];
+        cse.clear();                                   // ids changed; the graph is final at this point
+        return dropped;
     }
     int depth() const {
         int d = 0;

@@ -214,6 +214,7 @@ int fhs_prog_build(const char *op, const uint32_t *n_chars, size_t n_strings, si
         Builder B(*p, nbc, nbu);
         int rc = build_op(op, B, n_chars, n_strings, n_usize_args, scalars, n_scalars);
         if (rc != FHS_OK) { delete p; return rc; }
+        p->g.prune(p->outputs);     // evaluations no output depends on (duplicates are merged at creation)
     } catch (const std::exception &e) {
         g_host_err = std::string("building ") + op + ": " + e.what();
         delete p;
