@@ -102,7 +102,27 @@ public:
             int64_t v = (x >= 0) ? (int64_t)(f((int)x) & 31) : -(int64_t)(f((int)(x + 16)) & 31);
             return constant(v);
         }
-        int id = lut_fn(f);
+        // a table applied to a*y + c where y is itself the output of a table on some linear combination L is ONE
+        // table on L: one level less on that path, and one evaluation less when y has no other reader
+        if (!signed_in && e.t.size() == 1 && nodes[e.t[0].src].kind == K_PBS && !nodes[e.t[0].src].signed_in) {
+            const Node sn = nodes[e.t[0].src];
+            const Table &t1 = luts[sn.lut];
+            Table g2;
+            for (int v = 0; v < 16; v++) {
+                const int64_t u = ((int64_t)e.t[0].coef * (int64_t)t1[v] + e.c) & 31;
+                g2[v] = u < 16 ? ((uint64_t)f((int)u) & 31u) : 0u;    // u >= 16: not reachable for an unsigned input
+            }
+            Lin inner;
+            inner.t.assign(terms.begin() + sn.t0, terms.begin() + sn.t0 + sn.tn);
+            inner.c = sn.c;
+            inner.lo = sn.in_lo;
+            inner.hi = sn.in_hi;
+            inner.noise = 0.f;                  // already counted when the inner evaluation was made
+            return pbs_table(inner, lut(g2), out_lo, out_hi, false);
+        }
+        return pbs_table(e, lut_fn(f), out_lo, out_hi, signed_in);
+    }
+    Lin pbs_table(const Lin &e, int id, int out_lo, int out_hi, bool signed_in) {
         // common-subexpression elimination: the same table on the same linear combination is one evaluation
         // (the builders ask again for zero masks, equality bits, ... from several helpers: 35 % of split-256)
         std::vector<int64_t> key = cse_key(K_PBS, id, signed_in, e);
@@ -126,7 +146,7 @@ public:
             fprintf(stderr, "noise %.0f terms %zu lvl %d coefs:", e.noise, e.t.size(), level_of(e) + 1);
             for (size_t q = 0; q < e.t.size() && q < 12; q++) fprintf(stderr, " %d", e.t[q].coef);
             fprintf(stderr, " lut:");
-            for (int x = 0; x < 16; x++) fprintf(stderr, "%d,", (int)(f(x) & 31));
+            for (int x = 0; x < 16; x++) fprintf(stderr, "%d,", (int)(luts[id][x] & 31));
             fprintf(stderr, "\n");
         }
 #endif
