@@ -234,6 +234,25 @@ struct Ops {
         }
         return r;
     }
+    // c ? a : b with ONE evaluation per block, for chains of selections on the same operands (barrel shifters).
+    // c7 = 7 c (bit7 below makes it with the evaluation that would have made c).  x = c7 + (a - b) + 3 lies in
+    // [0, 13] and determines (c, a - b); the table x >= 7 ? x - 10 : 0 returns c (a - b) in [-3, 3]; the result is
+    // b + that, linear.  It carries b's noise + 1, so a chain must END with if_then_else (two evaluations per
+    // block, fresh result); a link whose input would exceed the linear-combination budget throws.
+    Rad mux7(const Bool &c7, const Rad &a, const Rad &b) {
+        Rad r;
+        for (size_t i = 0; i < a.size(); i++) {
+            const bool az = a[i].is_const() && a[i].c == 0, bz = b[i].is_const() && b[i].c == 0;
+            if (az && bz) { r.push_back(Graph::constant(0)); continue; }
+            if (c7.noise + a[i].noise + b[i].noise > kMaxLinNoise) throw std::logic_error("mux7: chain too long, refresh with if_then_else");
+            if (az) { r.push_back(g.pbs(add(c7, b[i]), [](int x) { return x < 7 ? x : 0; }, 0, 3)); continue; }
+            if (bz) { r.push_back(g.pbs(add(c7, a[i]), [](int x) { return x >= 7 ? x - 7 : 0; }, 0, 3)); continue; }
+            Lin x = bounded(addc(add(c7, sub(a[i], b[i])), 3), 0, 13);
+            Lin f = g.pbs(x, [](int v) { return v >= 7 ? v - 10 : 0; }, -3, 3);
+            r.push_back(bounded(add(b[i], f), 0, 3));
+        }
+        return r;
+    }
     Bool if_then_else_bool(const Bool &c, const Bool &a, const Bool &b) {
         // 4c + 2a + b <= 7
         return g.pbs(add(add(scale(c, 4), scale(a, 2)), b), [](int x) { return x >= 4 ? ((x >> 1) & 1) : (x & 1); }, 0, 1);
@@ -345,6 +364,8 @@ struct Ops {
     // low bit / high bit of a clean block
     Bool bit0(const Lin &blk) { return g.pbs(blk, [](int x) { return x & 1; }, 0, 1); }
     Bool bit1(const Lin &blk) { return g.pbs(blk, [](int x) { return (x >> 1) & 1; }, 0, 1); }
+    // bit `bit` of a base-4 digit as 0 / 7: the condition operand of mux7
+    Bool bit7(const Lin &blk, int bit) { return g.pbs(blk, [bit](int x) { return ((x >> bit) & 1) ? 7 : 0; }, 0, 7); }
 };
 
 }  // namespace fhs_host

@@ -41,18 +41,28 @@ struct ReplaceOps : SplitOps {
         std::vector<Rad> cur(cap, z);
         for (size_t j = 0; j < std::min(cap, b.size()); j++) cur[j] = b[j];
         std::vector<Bool> overflow;
+        // the last in-range stage is a two-evaluation selection (fresh result: what concat adds to A must not
+        // bring a chain's noise along), the ones before it are one-evaluation mux7 links
+        auto dead_bit = [&](size_t blk, int bit) { return amount[blk].is_const() && ((amount[blk].c >> bit) & 1) == 0; };
+        int last_blk = -1, last_bit = -1;
+        for (size_t blk = 0; blk < amount.size(); blk++)
+            for (int bit = 0; bit < 2; bit++) {
+                const size_t sh = (size_t)1 << (2 * blk + bit);
+                if (sh <= max_amount && sh < cap && !dead_bit(blk, bit)) { last_blk = (int)blk; last_bit = bit; }
+            }
         for (size_t blk = 0; blk < amount.size(); blk++) {
             for (int bit = 0; bit < 2; bit++) {
                 const size_t sh = (size_t)1 << (2 * blk + bit);
                 if (sh > max_amount) break;
-                Bool sb = bit ? bit1(amount[blk]) : bit0(amount[blk]);
-                if (sb.is_const() && sb.c == 0) continue;
-                if (sh >= cap) { overflow.push_back(sb); continue; }
+                if (dead_bit(blk, bit)) continue;
+                if (sh >= cap) { overflow.push_back(bit ? bit1(amount[blk]) : bit0(amount[blk])); continue; }
+                const bool fresh = ((int)blk == last_blk && bit == last_bit) || amount[blk].is_const();
+                Bool sb = fresh ? (bit ? bit1(amount[blk]) : bit0(amount[blk])) : bit7(amount[blk], bit);
                 std::vector<Rad> nx(cap);
                 for (size_t j = 0; j < cap; j++) {
                     const Rad &from = (j >= sh) ? cur[j - sh] : z;
                     if (rad_is_zero_const(from) && rad_is_zero_const(cur[j])) { nx[j] = z; continue; }
-                    nx[j] = if_then_else(sb, from, cur[j]);
+                    nx[j] = fresh ? if_then_else(sb, from, cur[j]) : mux7(sb, from, cur[j]);
                 }
                 cur.swap(nx);
             }

@@ -194,6 +194,11 @@ struct StrOps : Ops {
         FStr cur = a;
         const size_t L1 = a.ch.size();
         Rad z = zero_char();
+        // the last in-range stage is a two-evaluation selection (fresh result), the ones before it mux7 links
+        int last_blk = -1, last_bit = -1;
+        for (size_t blk = 0; blk < idx.size(); blk++)
+            for (int bit = 0; bit < 2; bit++)
+                if (((size_t)1 << (2 * blk + bit)) < L1 && !(idx[blk].is_const() && ((idx[blk].c >> bit) & 1) == 0)) { last_blk = (int)blk; last_bit = bit; }
         for (size_t blk = 0; blk < idx.size(); blk++) {
             for (int bit = 0; bit < 2; bit++) {
                 const size_t sh = (size_t)1 << (2 * blk + bit);
@@ -206,12 +211,13 @@ struct StrOps : Ops {
                     cur = nx;
                     continue;
                 }
-                Bool sb = bit ? bit1(idx[blk]) : bit0(idx[blk]);
-                if (sb.is_const() && sb.c == 0) continue;
+                if (idx[blk].is_const() && ((idx[blk].c >> bit) & 1) == 0) continue;
+                const bool fresh = ((int)blk == last_blk && bit == last_bit) || idx[blk].is_const();
+                Bool sb = fresh ? (bit ? bit1(idx[blk]) : bit0(idx[blk])) : bit7(idx[blk], bit);
                 FStr nx;
                 for (size_t i = 0; i < L1; i++) {
                     const Rad &sh_c = (i + sh < L1) ? cur.ch[i + sh] : z;
-                    nx.ch.push_back(if_then_else(sb, sh_c, cur.ch[i]));
+                    nx.ch.push_back(fresh ? if_then_else(sb, sh_c, cur.ch[i]) : mux7(sb, sh_c, cur.ch[i]));
                 }
                 cur = nx;
             }
