@@ -22,6 +22,7 @@ struct fhs_prog {
     std::vector<int64_t> outputs;  // node id, or -1-c for a clear constant c
     std::string desc;
     size_t n_inputs = 0;
+    float max_output_noise = 0.f;  // largest variance multiplier (PBS outputs) an output block carries
 };
 
 namespace {
@@ -49,6 +50,7 @@ struct Builder {
     }
     void out_lin(const Lin &e) {
         if (e.is_const()) { P.outputs.push_back(-1 - (e.c & 31)); return; }
+        if (e.noise > P.max_output_noise) P.max_output_noise = e.noise;
         P.outputs.push_back(P.g.materialize(e));
     }
     void out_rad(const Rad &r) { for (auto &b : r) out_lin(b); }
@@ -266,6 +268,8 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
 // PBS (or is materialised), lo / hi bound the node's output, signed_in marks PBS nodes whose input may be
 // negative.  The test suite's clear-text evaluator asserts them, so that a wrong `bounded()`
 // override in the op builders fails at the node where it happens.
+double fhs_prog_output_noise(const fhs_prog *p) { return p ? (double)p->max_output_noise : -1.0; }
+
 int fhs_prog_export_ranges(const fhs_prog *p, int32_t *in_lo, int32_t *in_hi, int32_t *out_lo, int32_t *out_hi,
                            uint8_t *signed_in) {
     if (!p || !in_lo || !in_hi || !out_lo || !out_hi || !signed_in) return FHS_ERR_INVALID;

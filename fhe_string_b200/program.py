@@ -39,6 +39,8 @@ def load_host_library():
     L.fhs_prog_run_sharded.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int, ctypes.c_int, sz, vp, vp]
     L.fhs_prog_plan.argtypes = [vp, ctypes.c_int, ctypes.c_int, sz, vp, sz, ctypes.POINTER(sz)]
     L.fhs_prog_export_schedule.argtypes = [vp, ctypes.c_int, sz, vp, vp]
+    L.fhs_prog_output_noise.argtypes = [vp]
+    L.fhs_prog_output_noise.restype = ctypes.c_double
     _lib = L
     return L
 
@@ -78,6 +80,7 @@ class Program:
         (self.n_nodes, self.n_inputs, self.n_outputs, self.n_terms, self.n_luts, self.depth, self.pbs_count,
          self.max_noise) = [int(x) for x in info]
         self.desc = self.L.fhs_prog_output_desc(self.h).decode()
+        self.output_noise = float(self.L.fhs_prog_output_noise(self.h))
         self.nb_char, self.nb_usize = num_blocks_char, num_blocks_usize
 
     def __del__(self):

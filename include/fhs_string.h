@@ -55,6 +55,10 @@ int fhs_prog_export(const fhs_prog *p, uint8_t *kind, int32_t *lut, uint32_t *t0
                     int64_t *cst, int32_t *level, int32_t *term_src, int32_t *term_coef,
                     uint64_t *luts, int64_t *outputs);
 
+/* Largest variance multiplier (in units of one PBS output) any output block of the program carries.  The next
+ * operation treats its operands as fresh (1), so the builders keep this small (outputs above 4 are refreshed). */
+double fhs_prog_output_noise(const fhs_prog *p);
+
 /* Per node: bounds of the linear combination feeding it (in_lo, in_hi), of its output (out_lo, out_hi),
  * and whether a PBS input may be negative (negacyclic use of the padding bit).  For evaluators that
  * assert the builder's range claims. */

@@ -114,3 +114,27 @@ def test_no_table_directly_on_a_table(op, n_chars, kw):
         if kind[i] == 1 and tn[i] == 1 and not sg[i]:
             s = src[t0[i]]
             assert not (kind[s] == 1 and not sg[s]), f"node {i} is a table on table {s}"
+
+
+NOISE_CASES = CASES + [("len", (65,), {}), ("add", (33, 33), {}), ("insert", (33, 9), dict(n_usize_args=1, scalars=(64,))),
+                       ("repeat", (9,), dict(n_usize_args=1, scalars=(4,))), ("replace", (257, 3, 2), dict(scalars=(256,), num_blocks_usize=5)),
+                       ("splitn", (65, 9), dict(n_usize_args=1)), ("eq_ignore_ascii_case", (65, 65), {})]
+
+
+@pytest.mark.parametrize("op,n_chars,kw", NOISE_CASES)
+def test_chained_operations_stay_inside_the_noise_budget(op, n_chars, kw):
+    """An operation treats its operands as fresh (variance multiplier 1), but the previous operation may hand it
+    blocks that carry up to `output_noise` PBS-output variances.  Two bounds keep chains inside the budget of
+    DESIGN.md section 4: outputs carry at most 12, and operand blocks enter a table with sum(coef^2) <= 34
+    (the eq / bivariate packs), so a chained table input is at most 163 + 34 * 11 = 537 PBS-output variances =
+    3.6e-7 on top of 4.74e-6 of keyswitch + modulus-switch noise (z 7.175 -> 6.92, 2^-37.7 per evaluation)."""
+    prog = Program(op, n_chars=n_chars, **kw)
+    assert prog.output_noise <= 12, prog.output_noise
+    d = prog.export()
+    kind, t0, tn, src, coef = d["kind"], d["t0"], d["tn"], d["term_src"], d["term_coef"].astype(np.int64)
+    worst = 0
+    for i in np.where(kind == 1)[0]:
+        s, c = src[t0[i]:t0[i] + tn[i]], coef[t0[i]:t0[i] + tn[i]]
+        worst = max(worst, int((c[kind[s] == 0] ** 2).sum()))
+    assert worst <= 34, worst
+    assert prog.max_noise <= 163
