@@ -414,6 +414,66 @@ static std::vector<int32_t> balance_levels(const Graph &g, int world, size_t sha
         const double ms = total_ms(cand);
         if (ms < best_ms - 1e-9) { best_ms = ms; lvl.swap(cand); }
     }
+    // Second pass on the better schedule: two-level lookahead.  Moving k evaluations from level l to l + 1 may only
+    // pay once k2 evaluations of the (grown) level l + 1 move on to l + 2; the pairwise sweeps above never take
+    // the first half of such a move.  Same validity rule, gain measured over the three levels.
+    {
+        std::vector<std::vector<int32_t>> at(D + 3);
+        for (size_t i = 0; i < N; i++)
+            if (g.nodes[i].kind == K_PBS) at[lvl[i]].push_back((int32_t)i);
+        auto free_at = [&](int32_t i, int l) {       // may node i (at level l) move to l + 1 ?
+            for (int32_t c : readers[i]) if (lvl[c] < l + 2) return false;
+            return true;
+        };
+        for (int round = 0; round < 4; round++) {
+            bool any = false;
+            for (int l = 1; l + 2 <= D; l++) {
+                std::vector<int32_t> mv;
+                for (int32_t i : at[l]) if (free_at(i, l)) mv.push_back(i);
+                if (mv.empty()) continue;
+                const size_t b0 = at[l].size(), b1 = at[l + 1].size(), b2 = at[l + 2].size();
+                const double before = level_ms(b0, world, shard_min) + level_ms(b1, world, shard_min) + level_ms(b2, world, shard_min);
+                double best = 1e-9;
+                size_t best_k = 0, best_k2 = 0;
+                for (size_t tgt : targets(b0)) {
+                    const size_t k = b0 - tgt;
+                    if (k == 0 || k > mv.size()) continue;
+                    for (size_t q = 0; q < k; q++) lvl[mv[q]] = l + 1;          // tentatively
+                    size_t n2 = 0;                                               // how many of level l + 1 could move on
+                    for (int32_t i : at[l + 1]) if (free_at(i, l + 1)) n2++;
+                    for (size_t q = 0; q < k; q++) if (free_at(mv[q], l + 1)) n2++;
+                    const size_t b1k = b1 + k;
+                    std::vector<size_t> t2 = targets(b1k);
+                    t2.push_back(b1k);                                           // k2 = 0
+                    for (size_t tgt2 : t2) {
+                        const size_t k2 = b1k - tgt2;
+                        if (k2 > n2) continue;
+                        const double gain = before - level_ms(b0 - k, world, shard_min) - level_ms(b1k - k2, world, shard_min) -
+                                            level_ms(b2 + k2, world, shard_min);
+                        if (gain > best) { best = gain; best_k = k; best_k2 = k2; }
+                    }
+                    for (size_t q = 0; q < k; q++) lvl[mv[q]] = l;               // undo
+                }
+                if (!best_k) continue;
+                std::vector<int32_t> moved(mv.begin(), mv.begin() + best_k), keep;
+                for (int32_t i : at[l]) if (!std::binary_search(moved.begin(), moved.end(), i)) keep.push_back(i);
+                at[l].swap(keep);
+                for (int32_t i : moved) { lvl[i] = l + 1; at[l + 1].push_back(i); }
+                std::sort(at[l + 1].begin(), at[l + 1].end());
+                if (best_k2) {
+                    std::vector<int32_t> mv2, keep2;
+                    for (int32_t i : at[l + 1]) if (mv2.size() < best_k2 && free_at(i, l + 1)) mv2.push_back(i);
+                    for (int32_t i : at[l + 1]) if (!std::binary_search(mv2.begin(), mv2.end(), i)) keep2.push_back(i);
+                    at[l + 1].swap(keep2);
+                    for (int32_t i : mv2) { lvl[i] = l + 2; at[l + 2].push_back(i); }
+                    std::sort(at[l + 2].begin(), at[l + 2].end());
+                }
+                any = true;
+            }
+            if (!any) break;
+        }
+        best_ms = total_ms(lvl);
+    }
     // linear nodes follow their sources; then check every edge (fall back to the builder's levels on any doubt)
     for (size_t i = 0; i < N; i++) {
         const Node &n = g.nodes[i];
