@@ -2,6 +2,8 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <climits>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -343,6 +345,21 @@ static std::vector<int32_t> balance_levels(const Graph &g, int world, size_t sha
     }
     for (auto &r : readers) { std::sort(r.begin(), r.end()); r.erase(std::unique(r.begin(), r.end()), r.end()); }
     const size_t unit = world > 1 ? (size_t)world : 1;
+    // movable evaluations are taken in order of the room they still have (earliest reader furthest away first),
+    // so that what moves now can move again later; ties by node id
+    bool use_room = false;      // the whole search runs twice, with and without this ordering; the better one is kept
+    auto by_room = [&](std::vector<int32_t> &mv, const std::vector<int32_t> &lv) {
+        if (!use_room) return;
+        std::vector<std::pair<int32_t, int32_t>> key;
+        key.reserve(mv.size());
+        for (int32_t i : mv) {
+            int32_t first = INT32_MAX;
+            for (int32_t c : readers[i]) first = std::min(first, lv[c]);
+            key.emplace_back(-first, i);
+        }
+        std::sort(key.begin(), key.end());
+        for (size_t q = 0; q < mv.size(); q++) mv[q] = key[q].second;
+    };
     auto targets = [&](size_t b) {
         std::vector<size_t> v;
         static const size_t tiers[5] = {74, 148, 296, 370, 592};
@@ -393,7 +410,9 @@ static std::vector<int32_t> balance_levels(const Graph &g, int world, size_t sha
                     if (gain > best) { best = gain; best_k = k; }
                 }
                 if (!best_k) continue;
-                mv.resize(best_k);                      // ascending node ids
+                by_room(mv, lvl);
+                mv.resize(best_k);
+                std::sort(mv.begin(), mv.end());        // ascending node ids
                 std::vector<int32_t> keep;
                 keep.reserve(b - best_k);
                 for (int32_t i : cur)
@@ -407,6 +426,10 @@ static std::vector<int32_t> balance_levels(const Graph &g, int world, size_t sha
         }
         return lvl;
     };
+    std::vector<int32_t> final_lvl = asap;
+    double final_ms = total_ms(asap);
+    for (int order = 0; order < 2; order++) {
+    use_room = order == 1;
     std::vector<int32_t> lvl = asap;
     double best_ms = total_ms(asap);
     for (int strategy = 0; strategy < 2; strategy++) {
@@ -431,6 +454,7 @@ static std::vector<int32_t> balance_levels(const Graph &g, int world, size_t sha
                 std::vector<int32_t> mv;
                 for (int32_t i : at[l]) if (free_at(i, l)) mv.push_back(i);
                 if (mv.empty()) continue;
+                by_room(mv, lvl);
                 const size_t b0 = at[l].size(), b1 = at[l + 1].size(), b2 = at[l + 2].size();
                 const double before = level_ms(b0, world, shard_min) + level_ms(b1, world, shard_min) + level_ms(b2, world, shard_min);
                 double best = 1e-9;
@@ -456,13 +480,17 @@ static std::vector<int32_t> balance_levels(const Graph &g, int world, size_t sha
                 }
                 if (!best_k) continue;
                 std::vector<int32_t> moved(mv.begin(), mv.begin() + best_k), keep;
+                std::sort(moved.begin(), moved.end());
                 for (int32_t i : at[l]) if (!std::binary_search(moved.begin(), moved.end(), i)) keep.push_back(i);
                 at[l].swap(keep);
                 for (int32_t i : moved) { lvl[i] = l + 1; at[l + 1].push_back(i); }
                 std::sort(at[l + 1].begin(), at[l + 1].end());
                 if (best_k2) {
                     std::vector<int32_t> mv2, keep2;
-                    for (int32_t i : at[l + 1]) if (mv2.size() < best_k2 && free_at(i, l + 1)) mv2.push_back(i);
+                    for (int32_t i : at[l + 1]) if (free_at(i, l + 1)) mv2.push_back(i);
+                    by_room(mv2, lvl);
+                    mv2.resize(best_k2);
+                    std::sort(mv2.begin(), mv2.end());
                     for (int32_t i : at[l + 1]) if (!std::binary_search(mv2.begin(), mv2.end(), i)) keep2.push_back(i);
                     at[l + 1].swap(keep2);
                     for (int32_t i : mv2) { lvl[i] = l + 2; at[l + 2].push_back(i); }
@@ -474,6 +502,10 @@ static std::vector<int32_t> balance_levels(const Graph &g, int world, size_t sha
         }
         best_ms = total_ms(lvl);
     }
+    if (best_ms < final_ms - 1e-9) { final_ms = best_ms; final_lvl.swap(lvl); }
+    }
+    std::vector<int32_t> lvl = final_lvl;
+    const double best_ms = final_ms;
     // linear nodes follow their sources; then check every edge (fall back to the builder's levels on any doubt)
     for (size_t i = 0; i < N; i++) {
         const Node &n = g.nodes[i];
