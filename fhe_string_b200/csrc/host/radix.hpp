@@ -253,6 +253,12 @@ struct Ops {
         }
         return r;
     }
+    // would a mux7 link on these operands stay inside the linear-combination budget?  (c7 is a fresh evaluation)
+    static bool mux7_fits(const std::vector<Rad> &xs) {
+        float worst = 0.f;
+        for (auto &r : xs) for (auto &blk : r) worst = std::max(worst, blk.noise);
+        return 1.f + 2.f * worst <= kMaxLinNoise;
+    }
     Bool if_then_else_bool(const Bool &c, const Bool &a, const Bool &b) {
         // 4c + 2a + b <= 7
         return g.pbs(add(add(scale(c, 4), scale(a, 2)), b), [](int x) { return x >= 4 ? ((x >> 1) & 1) : (x & 1); }, 0, 1);

@@ -56,7 +56,7 @@ struct ReplaceOps : SplitOps {
                 if (sh > max_amount) break;
                 if (dead_bit(blk, bit)) continue;
                 if (sh >= cap) { overflow.push_back(bit ? bit1(amount[blk]) : bit0(amount[blk])); continue; }
-                const bool fresh = ((int)blk == last_blk && bit == last_bit) || amount[blk].is_const();
+                const bool fresh = ((int)blk == last_blk && bit == last_bit) || amount[blk].is_const() || !mux7_fits(cur);
                 Bool sb = fresh ? (bit ? bit1(amount[blk]) : bit0(amount[blk])) : bit7(amount[blk], bit);
                 std::vector<Rad> nx(cap);
                 for (size_t j = 0; j < cap; j++) {

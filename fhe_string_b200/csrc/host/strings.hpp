@@ -212,7 +212,8 @@ struct StrOps : Ops {
                     continue;
                 }
                 if (idx[blk].is_const() && ((idx[blk].c >> bit) & 1) == 0) continue;
-                const bool fresh = ((int)blk == last_blk && bit == last_bit) || idx[blk].is_const();
+                // (a chain that has used up the noise budget -- very long strings -- is refreshed in between)
+                const bool fresh = ((int)blk == last_blk && bit == last_bit) || idx[blk].is_const() || !mux7_fits(cur.ch);
                 Bool sb = fresh ? (bit ? bit1(idx[blk]) : bit0(idx[blk])) : bit7(idx[blk], bit);
                 FStr nx;
                 for (size_t i = 0; i < L1; i++) {
