@@ -5,6 +5,7 @@
 // tests/split.rs:33-47), without special cases.  The greedy non-overlap decision is the only serial
 // part: one PBS of depth per position.
 #pragma once
+#include <cstdlib>
 #include <functional>
 #include <map>
 
@@ -37,10 +38,10 @@ struct SplitOps : StrOps {
     }
     // The scan is a finite automaton whose state is the distance h to the nearest earlier chosen
     // match (h < M matters, anything else = "none").  For M <= 8 the positions are cut into chunks of
-    // ~sqrt(2 L) and every chunk after the first is scanned for ALL M possible entry states at once
+    // ~sqrt(L) and every chunk after the first is scanned for ALL M possible entry states at once
     // (the hypothetical history is a plaintext constant); the true entry state of chunk j, a one-hot
     // over h read off the resolved tail of chunk j-1, then selects among the M candidate results.
-    // Depth: chunk + 2 per chunk boundary instead of one level per position.
+    // Depth: chunk + 1 per chunk boundary instead of one level per position.
     static constexpr size_t kSpecMaxPattern = 8;
     std::vector<Bool> non_overlapping(const std::vector<Bool> &m, const std::vector<Bool> &bz, bool reverse) {
         const size_t L1 = m.size();
@@ -50,7 +51,7 @@ struct SplitOps : StrOps {
         std::vector<Bool> chosen(L1);
         auto at = [&](size_t k) -> size_t { return reverse ? L1 - 1 - k : k; };
         size_t chunk = 1;
-        while (chunk * chunk < 2 * L1) chunk++;
+        while (chunk * chunk < L1) chunk++;     // depth ~ chunk + L / chunk: one level per chunk boundary
         if (chunk < M) chunk = M;
         if (M > kSpecMaxPattern || L1 < 2 * chunk + 2) {
             for (size_t k = 0; k < L1; k++)
@@ -78,23 +79,26 @@ struct SplitOps : StrOps {
             cands.push_back(cd);
         }
         for (auto &cd : cands) {
-            // entry state: hot[h] = act[p0-h] && none of act[p0-1 .. p0-h+1]; hot[0] = no chosen within M-1
-            std::vector<Bool> hot(M);
-            Lin seen = Graph::constant(0), any_hot = Graph::constant(0);
+            // entry state h is "hot" iff e[h] == 1, with LINEAR e[h] <= 1:
+            //   e[h] = act[p0-h] - (act[p0-1] + .. + act[p0-h+1])   (h >= 1: chosen at distance h, nothing nearer)
+            //   e[0] = 1 - (act[p0-1] + .. + act[p0-M+1])            (nothing chosen within M-1)
+            // so "hot[h] and candidate" is the single signed table [e[h] + c == 2]: one level per chunk boundary
+            // (round 1 made hot[h] with one table and the AND with a second one)
+            std::vector<Lin> e(M);
+            Lin seen = Graph::constant(0);
             for (size_t h = 1; h < M; h++) {
                 const Bool &a = act[cd.p0 - h];
-                if (h == 1) hot[h] = a;
-                else hot[h] = g.pbs(sub(a, seen), [](int v) { return v == 1; }, 0, 1, true);
+                e[h] = bounded(sub(a, seen), -(int)(h - 1), 1);
                 seen = add(seen, a);
-                any_hot = add(any_hot, hot[h]);
             }
-            hot[0] = bounded(sub(Graph::constant(1), any_hot), 0, 1);
+            e[0] = bounded(sub(Graph::constant(1), seen), 2 - (int)M, 1);
             for (size_t k = cd.p0; k < cd.p1; k++) {
                 Lin v = Graph::constant(0);
                 for (size_t h = 0; h < M; h++) {
                     const Bool &c = cd.c[h][k - cd.p0];
-                    if (c.is_const()) { if (c.c) v = add(v, hot[h]); continue; }
-                    v = add(v, band(hot[h], c));
+                    if (c.is_const() && c.c == 0) continue;
+                    Lin x = add(e[h], c);
+                    v = add(v, g.pbs(bounded(x, e[h].lo, 2), [](int t) { return t == 2; }, 0, 1, true));
                 }
                 act[k] = bounded(v, 0, 1);
             }
